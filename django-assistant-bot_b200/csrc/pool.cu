@@ -1,0 +1,260 @@
+// pool.cu - fused masked mean-pool + L2 normalise of encoder hidden states.
+//
+// Stands behind assistant/ai/embedders/transformers.py:25 of the reference
+// (`outputs.last_hidden_state.mean(dim=1)`), generalised to a padded batch (masked mean)
+// and followed by the L2 normalisation the cosine consumer makes harmless.
+//
+// One pass over [B,T,D]: HBM-bound streaming, 128-bit loads, fp32 accumulation.
+// Grid = (S, B) with a thread-block cluster of S CTAs along x: the S CTAs of a cluster
+// split the token axis of one text, reduce through distributed shared memory, and the
+// cluster's rank-0 CTA normalises and writes the row.  S is picked so that B*S covers
+// the 148 SMs a few times even for small batches.
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace dab {
+
+namespace {
+
+constexpr int kPoolThreads = 256;
+
+__device__ __forceinline__ bool mask_on(const void *mask, int mask_dtype, long long i) {
+    if (mask == nullptr) return true;
+    switch (mask_dtype) {
+        case DAB_MASK_U8: return static_cast<const uint8_t *>(mask)[i] != 0;
+        case DAB_MASK_I32: return static_cast<const int32_t *>(mask)[i] != 0;
+        default: return static_cast<const long long *>(mask)[i] != 0;
+    }
+}
+
+__device__ __forceinline__ uint4 ld_stream(const uint4 *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+template <bool BF16>
+struct Vec;
+template <>
+struct Vec<false> {  // 4 fp32 per 16 bytes
+    static constexpr int kElems = 4;
+    __device__ static __forceinline__ void add(float *acc, const uint4 &v) {
+        acc[0] += __uint_as_float(v.x);
+        acc[1] += __uint_as_float(v.y);
+        acc[2] += __uint_as_float(v.z);
+        acc[3] += __uint_as_float(v.w);
+    }
+};
+template <>
+struct Vec<true> {  // 8 bf16 per 16 bytes
+    static constexpr int kElems = 8;
+    __device__ static __forceinline__ void add(float *acc, const uint4 &v) {
+        acc[0] += bf16_lo(v.x);
+        acc[1] += bf16_hi(v.x);
+        acc[2] += bf16_lo(v.y);
+        acc[3] += bf16_hi(v.y);
+        acc[4] += bf16_lo(v.z);
+        acc[5] += bf16_hi(v.z);
+        acc[6] += bf16_lo(v.w);
+        acc[7] += bf16_hi(v.w);
+    }
+};
+
+// NV = 16-byte column vectors per thread (1 when D*elem <= 4 KiB, up to 4).
+template <bool BF16, int NV>
+__global__ void __launch_bounds__(kPoolThreads)
+pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ mask, int mask_dtype,
+                   float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, float *__restrict__ out_inv,
+                   int T, int D, int vecs_per_row, int row_groups) {
+    constexpr int VE = Vec<BF16>::kElems;
+    constexpr int U = 8 / NV;  // rows in flight per thread
+    extern __shared__ float smem[];
+    float *part = smem;                                    // [row_groups][D] partial sums of this CTA
+    float *psum = smem + (size_t)row_groups * D;           // [D] CTA total, read by rank 0 over DSMEM
+    __shared__ float s_red[kPoolThreads / 32];
+    __shared__ int s_cnt[kPoolThreads / 32];
+    __shared__ int s_count;                                // unmasked tokens in this CTA's slice
+    __shared__ float s_inv;
+
+    cg::cluster_group cluster = cg::this_cluster();
+    const int S = gridDim.x;
+    const int rank = blockIdx.x;
+    const long long b = blockIdx.y;
+    const int tid = threadIdx.x;
+    const int rg = tid / vecs_per_row * (NV == 1 ? 1 : 0);  // NV > 1 => one row group
+    const int c0 = NV == 1 ? tid % vecs_per_row : tid;
+    const bool active = NV == 1 ? (tid < row_groups * vecs_per_row) : true;
+
+    const int per = (T + S - 1) / S;
+    const int t0 = rank * per;
+    const int t1 = min(T, t0 + per);
+
+    float acc[NV][VE];
+#pragma unroll
+    for (int v = 0; v < NV; v++)
+#pragma unroll
+        for (int e = 0; e < VE; e++) acc[v][e] = 0.f;
+
+    if (active) {
+        const uint4 *base = hidden + (size_t)b * T * vecs_per_row;
+        for (int t = t0 + rg; t < t1; t += row_groups * U) {
+            uint4 vals[U][NV];
+            bool on[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int tt = t + u * row_groups;
+                on[u] = tt < t1 && mask_on(mask, mask_dtype, b * T + tt);
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                if (on[u]) {
+                    const uint4 *row = base + (size_t)(t + u * row_groups) * vecs_per_row;
+#pragma unroll
+                    for (int v = 0; v < NV; v++) {
+                        const int c = c0 + v * kPoolThreads;
+                        if (NV == 1 || c < vecs_per_row) vals[u][v] = ld_stream(row + c);
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                if (on[u]) {
+#pragma unroll
+                    for (int v = 0; v < NV; v++) {
+                        const int c = c0 + v * kPoolThreads;
+                        if (NV == 1 || c < vecs_per_row) Vec<BF16>::add(acc[v], vals[u][v]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int v = 0; v < NV; v++) {
+            const int c = c0 + v * kPoolThreads;
+            if (NV == 1 || c < vecs_per_row) {
+#pragma unroll
+                for (int e = 0; e < VE; e++) part[(size_t)rg * D + (size_t)c * VE + e] = acc[v][e];
+            }
+        }
+    }
+    // token count of this slice
+    int cnt = 0;
+    for (int tt = t0 + tid; tt < t1; tt += kPoolThreads) cnt += mask_on(mask, mask_dtype, b * T + tt) ? 1 : 0;
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if ((tid & 31) == 0) s_cnt[tid >> 5] = cnt;
+    __syncthreads();
+    if (tid == 0) {
+        int c = 0;
+        for (int w = 0; w < kPoolThreads / 32; w++) c += s_cnt[w];
+        s_count = c;
+    }
+    // fixed-order reduction over the row groups -> psum
+    for (int d = tid; d < D; d += kPoolThreads) {
+        float s = 0.f;
+        for (int g = 0; g < row_groups; g++) s += part[(size_t)g * D + d];
+        psum[d] = s;
+    }
+    cluster.sync();  // every CTA's psum / s_count is visible cluster-wide
+
+    if (rank == 0) {
+        int total = 0;
+        for (int r = 0; r < S; r++) total += *cluster.map_shared_rank(&s_count, r);
+        const float inv_cnt = 1.0f / (float)max(total, 1);
+        float ss = 0.f;
+        for (int d = tid; d < D; d += kPoolThreads) {
+            float s = 0.f;
+            for (int r = 0; r < S; r++) s += cluster.map_shared_rank(psum, r)[d];
+            s *= inv_cnt;
+            part[d] = s;  // reuse as the mean
+            ss += s * s;
+        }
+        ss = warp_sum(ss);
+        if ((tid & 31) == 0) s_red[tid >> 5] = ss;
+        __syncthreads();
+        if (tid == 0) {
+            float t = 0.f;
+            for (int w = 0; w < kPoolThreads / 32; w++) t += s_red[w];
+            s_inv = 1.0f / fmaxf(sqrtf(t), 1e-12f);
+        }
+        __syncthreads();
+        const float inv = s_inv;
+        for (int d = tid; d < D; d += kPoolThreads) {
+            const float o = part[d] * inv;
+            out[(size_t)b * D + d] = o;
+            if (out_bf16) out_bf16[(size_t)b * D + d] = __float2bfloat16_rn(o);
+        }
+        if (tid == 0 && out_inv) out_inv[b] = inv;
+    }
+    cluster.sync();  // keep remote shared memory alive until rank 0 has read it
+}
+
+template <bool BF16, int NV>
+int launch_pool(const void *hidden, const void *mask, int mask_dtype, float *out, void *out_bf16, float *out_inv,
+                int64_t B, int64_t T, int64_t D, int S, int vecs_per_row, int row_groups, cudaStream_t stream) {
+    auto kern = pool_l2norm_kernel<BF16, NV>;
+    const size_t smem = ((size_t)row_groups * D + D) * sizeof(float);
+    if (smem > 48 * 1024) DAB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(S, (unsigned)B, 1);
+    cfg.blockDim = dim3(kPoolThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = S;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, static_cast<const uint4 *>(hidden), mask, mask_dtype, out,
+                                   static_cast<__nv_bfloat16 *>(out_bf16), out_inv, (int)T, (int)D, vecs_per_row,
+                                   row_groups));
+    return DAB_OK;
+}
+
+}  // namespace
+
+// chosen so B*S fills the SMs ~3x when the batch is small, never slicing below 16 tokens per row group
+int pool_pick_splits(int64_t B, int64_t T, int row_groups) {
+    int S = 1;
+    while (S < 8 && B * S < 3 * 148 && T / (2 * S) >= 16 * row_groups) S *= 2;
+    return S;
+}
+
+}  // namespace dab
+
+extern "C" DAB_API int dab_pool_l2norm(const void *hidden, int hidden_dtype, const void *mask, int mask_dtype, float *out,
+                               void *out_bf16, float *out_inv, int64_t B, int64_t T, int64_t D, void *stream) {
+    using namespace dab;
+    if (!hidden || !out) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden/out must not be NULL");
+    if (hidden_dtype != DAB_F32 && hidden_dtype != DAB_BF16) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden_dtype must be DAB_F32 or DAB_BF16");
+    if (mask && (mask_dtype < DAB_MASK_U8 || mask_dtype > DAB_MASK_I64)) return fail(DAB_E_INVALID, "dab_pool_l2norm: bad mask_dtype");
+    if (B < 0 || T < 0 || D <= 0) return fail(DAB_E_INVALID, "dab_pool_l2norm: negative size");
+    if (B == 0) return DAB_OK;
+    if (B > 65535) return fail(DAB_E_INVALID, "dab_pool_l2norm: B > 65535, split the batch");
+    if (T > (1 << 24)) return fail(DAB_E_INVALID, "dab_pool_l2norm: T too large");
+    const int ve = hidden_dtype == DAB_BF16 ? 8 : 4;
+    if (D % ve) return fail(DAB_E_INVALID, "dab_pool_l2norm: D must be a multiple of 4 (fp32) / 8 (bf16)");
+    if (!aligned16(hidden) || !aligned16(out)) return fail(DAB_E_INVALID, "dab_pool_l2norm: pointers must be 16-byte aligned");
+    const int vecs = (int)(D / ve);
+    int nv = 1, row_groups = 1;
+    if (vecs <= kPoolThreads) {
+        row_groups = kPoolThreads / vecs;
+    } else {
+        nv = (vecs + kPoolThreads - 1) / kPoolThreads;
+        if (nv > 4) return fail(DAB_E_INVALID, "dab_pool_l2norm: D too large (max 4096 fp32 / 8192 bf16)");
+        if (nv == 3) nv = 4;
+    }
+    const int S = pool_pick_splits(B, T, row_groups);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool bf = hidden_dtype == DAB_BF16;
+#define DAB_POOL_CASE(BF, NV_) return launch_pool<BF, NV_>(hidden, mask, mask_dtype, out, out_bf16, out_inv, B, T, D, S, vecs, row_groups, st)
+    if (nv == 1) { if (bf) DAB_POOL_CASE(true, 1); else DAB_POOL_CASE(false, 1); }
+    if (nv == 2) { if (bf) DAB_POOL_CASE(true, 2); else DAB_POOL_CASE(false, 2); }
+    if (bf) DAB_POOL_CASE(true, 4); else DAB_POOL_CASE(false, 4);
+#undef DAB_POOL_CASE
+}

@@ -1,0 +1,58 @@
+// search.cuh - state shared by the scan kernels, the selection kernels and the store.
+#pragma once
+#include "common.cuh"
+
+namespace dab {
+
+// smallest key any real (finite-score) candidate beats: score -inf, row 0xffffffff
+constexpr uint64_t kTauMin = 0x007FFFFF00000000ull;
+
+// Per-store device scratch used by a search (allocated once in dab_store_create, or handed
+// in by the caller of the no-allocation entry point).  All arrays are sized for
+// DAB_MAX_QUERY_BATCH queries.
+struct SearchScratch {
+    float *qhat;            // [256, dim] unit-norm fp32 queries
+    __nv_bfloat16 *qsplit;  // [512, dim] bf16 hi rows then lo rows of qhat (tensor path)
+    uint64_t *cand;         // [256, kCandCap] candidate keys
+    uint32_t *cand_count;   // [256] appended this far (may exceed kCandCap: overflow)
+    uint64_t *tau_key;      // [256] current admission threshold (a kept candidate's key)
+    int *active;            // [256] query takes part in the current round
+    int *overflowed;        // [256] query overflowed in the current round
+    SearchCtrl *ctrl;
+};
+
+size_t search_scratch_bytes(int dim);
+// carve `base` (256-byte aligned, search_scratch_bytes(dim) long) into a SearchScratch
+SearchScratch carve_scratch(void *base, int dim);
+
+struct StoreView {
+    const void *rows;        // [n, dim] fp32 or bf16
+    const float *inv_norm;   // [n] (padded to a multiple of 4 with zeros)
+    const int64_t *ids;      // [n] or nullptr (implicit id_base + row)
+    int64_t id_base;
+    int64_t n;
+    int dim;
+    int dtype;
+};
+
+LevelPlan make_level_plan(int64_t n_rows, int tile_rows, int k_keep);
+
+// ---- kernels' host launchers (each returns DAB_OK or an error code) ----
+int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st);
+int launch_compact(const SearchScratch &sc, int nq, int k_keep, int num_levels, cudaStream_t st);
+int launch_finish_exact(const SearchScratch &sc, const StoreView &sv, int nq, int k, int num_levels, float *out_scores,
+                        int64_t *out_ids, cudaStream_t st);
+int launch_finish_rescore(const SearchScratch &sc, const StoreView &sv, int nq, int k, int k_keep, int num_levels,
+                          float *out_scores, int64_t *out_ids, cudaStream_t st);
+int launch_fill_empty(float *out_scores, int64_t *out_ids, int64_t count, cudaStream_t st);
+
+int simt_tile_rows(int dim, int dtype);
+int launch_scan_simt(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
+                     const LevelPlan &plan, int num_sms, cudaStream_t st);
+
+int umma_tile_rows();
+bool umma_supported(int dim, int dtype);
+int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int nq, bool split,
+                     const LevelPlan &plan, int num_sms, void *tensor_map_rows, void *tensor_map_q, cudaStream_t st);
+
+}  // namespace dab

@@ -1,0 +1,448 @@
+// select.cu - the selection side of the search: query preparation, per-round candidate
+// compaction (sort + dedupe + threshold update + on-device round control), the final
+// write-out (with exact fp32 rescoring for the tensor path) and the cross-shard k-way merge.
+//
+// Together with a scan kernel these implement what PostgreSQL does for
+// `ORDER BY embedding <=> q LIMIT n` (assistant/rag/services/search_service.py:192-194).
+#include "search.cuh"
+
+namespace dab {
+
+size_t search_scratch_bytes(int dim) {
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    size_t b = 0;
+    b += up((size_t)DAB_MAX_QUERY_BATCH * dim * sizeof(float));               // qhat
+    b += up((size_t)2 * DAB_MAX_QUERY_BATCH * dim * sizeof(__nv_bfloat16));   // qsplit
+    b += up((size_t)DAB_MAX_QUERY_BATCH * kCandCap * sizeof(uint64_t));       // cand
+    b += up(DAB_MAX_QUERY_BATCH * sizeof(uint32_t));                          // cand_count
+    b += up(DAB_MAX_QUERY_BATCH * sizeof(uint64_t));                          // tau_key
+    b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // active
+    b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // overflowed
+    b += up(sizeof(SearchCtrl));
+    return b;
+}
+
+SearchScratch carve_scratch(void *base, int dim) {
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    char *p = static_cast<char *>(base);
+    SearchScratch s;
+    s.qhat = reinterpret_cast<float *>(p);
+    p += up((size_t)DAB_MAX_QUERY_BATCH * dim * sizeof(float));
+    s.qsplit = reinterpret_cast<__nv_bfloat16 *>(p);
+    p += up((size_t)2 * DAB_MAX_QUERY_BATCH * dim * sizeof(__nv_bfloat16));
+    s.cand = reinterpret_cast<uint64_t *>(p);
+    p += up((size_t)DAB_MAX_QUERY_BATCH * kCandCap * sizeof(uint64_t));
+    s.cand_count = reinterpret_cast<uint32_t *>(p);
+    p += up(DAB_MAX_QUERY_BATCH * sizeof(uint32_t));
+    s.tau_key = reinterpret_cast<uint64_t *>(p);
+    p += up(DAB_MAX_QUERY_BATCH * sizeof(uint64_t));
+    s.active = reinterpret_cast<int *>(p);
+    p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
+    s.overflowed = reinterpret_cast<int *>(p);
+    p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
+    s.ctrl = reinterpret_cast<SearchCtrl *>(p);
+    return s;
+}
+
+// Levels: level l scans the tiles t with t % stride[l] == 0 not scanned before, stride[l] =
+// growth^(L-1-l).  Level 0 is a strided sample small enough that every row may pass
+// (<= kCandCap/2 rows); each later level is (growth-1) times everything before it, so with a
+// threshold equal to the k-th best seen so far about k*(growth-1) <= kCandCap/2 rows pass.
+LevelPlan make_level_plan(int64_t n_rows, int tile_rows, int k_keep) {
+    LevelPlan p = {};
+    p.tile_rows = tile_rows;
+    p.num_tiles = (n_rows + tile_rows - 1) / tile_rows;
+    int g = 32;
+    while (g > 2 && (long long)g * k_keep > kCandCap / 2) g >>= 1;
+    p.growth = g;
+    int L = 1;
+    long long s0 = 1;
+    while (L < kMaxLevels && ((p.num_tiles + s0 - 1) / s0) * tile_rows > kCandCap / 2) {
+        s0 *= g;
+        L++;
+    }
+    p.num_levels = L;
+    long long s = s0;
+    for (int l = 0; l < L; l++) {
+        p.stride[l] = (int)s;
+        const long long m = (p.num_tiles + s - 1) / s;
+        p.tiles_in_level[l] = l == 0 ? m : m - (m + g - 1) / g;
+        s /= g;
+    }
+    return p;
+}
+
+namespace {
+
+// ---------------------------------------------------------------- begin: normalise queries, reset state
+__global__ void __launch_bounds__(128)
+search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int want_split) {
+    const int qi = blockIdx.x;
+    const int tid = threadIdx.x;
+    __shared__ float red[4];
+    const float *src = q + (size_t)qi * dim;
+    float ss = 0.f;
+    for (int d = tid; d < dim; d += 128) {
+        const float v = src[d];
+        ss += v * v;
+    }
+    ss = warp_sum(ss);
+    if ((tid & 31) == 0) red[tid >> 5] = ss;
+    __syncthreads();
+    const float tot = red[0] + red[1] + red[2] + red[3];
+    const float inv = tot > 0.f ? 1.0f / sqrtf(tot) : 0.f;
+    for (int d = tid; d < dim; d += 128) {
+        const float v = src[d] * inv;
+        sc.qhat[(size_t)qi * dim + d] = v;
+        if (want_split) {
+            // q = hi + lo + r with |r| <= 2^-17 |q|: two bf16 MMAs recover the fp32 query
+            const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+            const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+            sc.qsplit[(size_t)qi * dim + d] = hi;
+            sc.qsplit[(size_t)(DAB_MAX_QUERY_BATCH + qi) * dim + d] = lo;
+        }
+    }
+    if (tid == 0) {
+        sc.cand_count[qi] = 0;
+        sc.tau_key[qi] = kTauMin;
+        sc.active[qi] = 1;
+        sc.overflowed[qi] = 0;
+        if (qi == 0) {
+            SearchCtrl c = {};
+            *sc.ctrl = c;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- bitonic sort of 64-bit keys, descending
+template <int THREADS>
+__device__ void bitonic_sort_desc(uint64_t *keys, int P) {
+    for (int size = 2; size <= P; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int i = threadIdx.x; i < (P >> 1); i += THREADS) {
+                const int lo = 2 * i - (i & (stride - 1));
+                const int hi = lo + stride;
+                const bool desc = (lo & size) == 0;
+                const uint64_t a = keys[lo], b = keys[hi];
+                if ((a < b) == desc) {
+                    keys[lo] = b;
+                    keys[hi] = a;
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+constexpr int kCompactThreads = 1024;
+
+// One CTA per query: sort this round's candidates, drop duplicates (a retried level re-adds
+// rows), keep the best k_keep, publish the new threshold; the last CTA to finish advances
+// (or repeats) the level - the host never has to look.
+__global__ void __launch_bounds__(kCompactThreads)
+compact_kernel(SearchScratch sc, int nq, int k_keep, int num_levels) {
+    extern __shared__ uint64_t keys[];  // [kCandCap]
+    __shared__ int s_scan[kCompactThreads / 32];
+    __shared__ int s_is_last;
+    const int qi = blockIdx.x;
+    const int tid = threadIdx.x;
+    SearchCtrl *ctrl = sc.ctrl;
+    const int level = ctrl->cur_level;
+    if (level < num_levels && sc.active[qi]) {
+        const uint32_t raw = sc.cand_count[qi];
+        const int n = (int)min(raw, (uint32_t)kCandCap);
+        const bool ovf = raw > (uint32_t)kCandCap;
+        int P = 32;
+        while (P < n) P <<= 1;
+        uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
+        for (int i = tid; i < P; i += kCompactThreads) keys[i] = i < n ? mine[i] : 0ull;
+        bitonic_sort_desc<kCompactThreads>(keys, P);
+        // dedupe + keep the first k_keep unique keys (block-wide exclusive scan of the "is new" flags)
+        int kept_total = 0;
+        for (int base = 0; base < n && kept_total < k_keep; base += kCompactThreads) {
+            const int i = base + tid;
+            const uint64_t me = i < n ? keys[i] : 0ull;
+            const int flag = (i < n && (i == 0 || keys[i - 1] != me)) ? 1 : 0;
+            const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+            const int lane = tid & 31, warp = tid >> 5;
+            if (lane == 0) s_scan[warp] = __popc(ballot);
+            __syncthreads();
+            int offset = kept_total;
+            for (int w = 0; w < warp; w++) offset += s_scan[w];
+            int block_total = 0;
+            for (int w = 0; w < kCompactThreads / 32; w++) block_total += s_scan[w];
+            const int pos = offset + __popc(ballot & ((1u << lane) - 1u));
+            if (flag && pos < k_keep) mine[pos] = me;
+            kept_total += block_total;
+            __syncthreads();
+        }
+        if (tid == 0) {
+            const int keep = min(kept_total, k_keep);
+            sc.cand_count[qi] = keep;
+            sc.overflowed[qi] = ovf ? 1 : 0;
+            if (ovf) atomicExch(&ctrl->any_overflow, 1);
+        }
+        __syncthreads();  // mine[0..keep) written by this block
+        if (tid == 0) {
+            const int keep = min(kept_total, k_keep);
+            // a threshold is only valid once k_keep real candidates exist
+            sc.tau_key[qi] = keep == k_keep ? mine[k_keep - 1] : kTauMin;
+        }
+    }
+    // ---- round control by the last CTA
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_is_last = (atomicAdd(&ctrl->ticket, 1u) == gridDim.x - 1) ? 1 : 0;
+    __syncthreads();
+    if (!s_is_last) return;
+    __threadfence();
+    const int any = *(volatile int *)&ctrl->any_overflow;
+    if (level < num_levels) {
+        for (int q = tid; q < nq; q += kCompactThreads) sc.active[q] = any ? sc.overflowed[q] : 1;
+    }
+    if (tid == 0) {
+        if (level < num_levels) {
+            if (any) {
+                ctrl->retry = 1;
+                ctrl->overflow_events += 1;
+            } else {
+                ctrl->retry = 0;
+                ctrl->cur_level = level + 1;
+            }
+            ctrl->rounds_run += 1;
+        }
+        ctrl->any_overflow = 0;
+        ctrl->ticket = 0;
+    }
+}
+
+// ---------------------------------------------------------------- finish (exact paths): keys -> outputs
+__global__ void __launch_bounds__(128)
+finish_exact_kernel(SearchScratch sc, StoreView sv, int k, int num_levels, float *__restrict__ out_scores,
+                    int64_t *__restrict__ out_ids) {
+    const int qi = blockIdx.x;
+    const bool done = sc.ctrl->cur_level >= num_levels;
+    const int cnt = done ? min((int)sc.cand_count[qi], k) : 0;
+    const uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
+    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+        float s;
+        int64_t id;
+        if (j < cnt) {
+            const uint64_t key = mine[j];
+            const uint32_t row = key_row(key);
+            s = key_score(key);
+            id = sv.ids ? sv.ids[row] : sv.id_base + (int64_t)row;
+        } else {
+            s = done ? -INFINITY : __int_as_float(0x7fc00000);
+            id = -1;
+        }
+        out_scores[(size_t)qi * k + j] = s;
+        out_ids[(size_t)qi * k + j] = id;
+    }
+}
+
+// ---------------------------------------------------------------- finish (tensor path): exact fp32 rescoring
+// The tensor pass ranks with approximate scores; the kept k_keep >= k candidates are rescored
+// here with the fp32 query on CUDA cores (fp32 FMA over the stored bf16 row, upcast exactly),
+// re-sorted under (score desc, row asc) and cut to k.
+constexpr int kRescoreThreads = 256;
+__global__ void __launch_bounds__(kRescoreThreads)
+finish_rescore_kernel(SearchScratch sc, StoreView sv, int k, int k_keep, int num_levels,
+                      float *__restrict__ out_scores, int64_t *__restrict__ out_ids) {
+    extern __shared__ uint64_t keys[];  // [pow2 >= k_keep]
+    const int qi = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool done = sc.ctrl->cur_level >= num_levels;
+    const int cnt = done ? min((int)sc.cand_count[qi], k_keep) : 0;
+    int P = 32;
+    while (P < cnt) P <<= 1;
+    const uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
+    const float *q = sc.qhat + (size_t)qi * sv.dim;
+    for (int i = tid; i < P; i += kRescoreThreads) keys[i] = 0ull;
+    __syncthreads();
+    for (int j = warp; j < cnt; j += kRescoreThreads / 32) {
+        const uint32_t row = key_row(mine[j]);
+        float acc = 0.f;
+        if (sv.dtype == DAB_BF16) {
+            const uint4 *r = reinterpret_cast<const uint4 *>(static_cast<const __nv_bfloat16 *>(sv.rows) + (size_t)row * sv.dim);
+            for (int c = lane; c < sv.dim / 8; c += 32) {
+                const uint4 v = r[c];
+                const float4 q0 = reinterpret_cast<const float4 *>(q)[2 * c];
+                const float4 q1 = reinterpret_cast<const float4 *>(q)[2 * c + 1];
+                acc = fmaf(bf16_lo(v.x), q0.x, acc);
+                acc = fmaf(bf16_hi(v.x), q0.y, acc);
+                acc = fmaf(bf16_lo(v.y), q0.z, acc);
+                acc = fmaf(bf16_hi(v.y), q0.w, acc);
+                acc = fmaf(bf16_lo(v.z), q1.x, acc);
+                acc = fmaf(bf16_hi(v.z), q1.y, acc);
+                acc = fmaf(bf16_lo(v.w), q1.z, acc);
+                acc = fmaf(bf16_hi(v.w), q1.w, acc);
+            }
+        } else {
+            const float4 *r = reinterpret_cast<const float4 *>(static_cast<const float *>(sv.rows) + (size_t)row * sv.dim);
+            for (int c = lane; c < sv.dim / 4; c += 32) {
+                const float4 v = r[c];
+                const float4 qq = reinterpret_cast<const float4 *>(q)[c];
+                acc = fmaf(v.x, qq.x, acc);
+                acc = fmaf(v.y, qq.y, acc);
+                acc = fmaf(v.z, qq.z, acc);
+                acc = fmaf(v.w, qq.w, acc);
+            }
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) keys[j] = make_key(acc * sv.inv_norm[row], row);
+    }
+    bitonic_sort_desc<kRescoreThreads>(keys, P);
+    const int outn = min(cnt, k);
+    for (int j = tid; j < k; j += kRescoreThreads) {
+        float s;
+        int64_t id;
+        if (j < outn) {
+            const uint64_t key = keys[j];
+            const uint32_t row = key_row(key);
+            s = key_score(key);
+            id = sv.ids ? sv.ids[row] : sv.id_base + (int64_t)row;
+        } else {
+            s = done ? -INFINITY : __int_as_float(0x7fc00000);
+            id = -1;
+        }
+        out_scores[(size_t)qi * k + j] = s;
+        out_ids[(size_t)qi * k + j] = id;
+    }
+}
+
+__global__ void fill_empty_kernel(float *out_scores, int64_t *out_ids, int64_t count) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) {
+        out_scores[i] = -INFINITY;
+        out_ids[i] = -1;
+    }
+}
+
+// ---------------------------------------------------------------- k-way merge of per-shard lists
+struct MergeItem {
+    uint32_t s;   // orderable score
+    int64_t id;   // < 0 = empty
+};
+__device__ __forceinline__ bool merge_better(const MergeItem &a, const MergeItem &b) {
+    const bool ae = a.id < 0, be = b.id < 0;
+    if (ae != be) return be;
+    if (a.s != b.s) return a.s > b.s;
+    return a.id < b.id;
+}
+constexpr int kMergeThreads = 256;
+constexpr int kMergeMax = 8192;
+__global__ void __launch_bounds__(kMergeThreads)
+merge_topk_kernel(const float *__restrict__ gs, const int64_t *__restrict__ gi, int R, int Q, int k,
+                  float *__restrict__ out_scores, int64_t *__restrict__ out_ids) {
+    extern __shared__ unsigned char smem_raw[];
+    uint32_t *ss = reinterpret_cast<uint32_t *>(smem_raw);
+    int n = R * k;
+    int P = 32;
+    while (P < n) P <<= 1;
+    int64_t *si = reinterpret_cast<int64_t *>(smem_raw + (size_t)P * sizeof(uint32_t));
+    const int qi = blockIdx.x;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < P; i += kMergeThreads) {
+        if (i < n) {
+            const int r = i / k, j = i % k;
+            const size_t src = ((size_t)r * Q + qi) * k + j;
+            const int64_t id = gi[src];
+            const float sc = gs[src];
+            si[i] = (id >= 0 && sc == sc) ? id : -1;
+            ss[i] = f32_orderable(sc);
+        } else {
+            si[i] = -1;
+            ss[i] = 0;
+        }
+    }
+    for (int size = 2; size <= P; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int i = tid; i < (P >> 1); i += kMergeThreads) {
+                const int lo = 2 * i - (i & (stride - 1));
+                const int hi = lo + stride;
+                const bool desc = (lo & size) == 0;
+                MergeItem a{ss[lo], si[lo]}, b{ss[hi], si[hi]};
+                if (merge_better(b, a) == desc && (a.s != b.s || a.id != b.id)) {
+                    ss[lo] = b.s; si[lo] = b.id;
+                    ss[hi] = a.s; si[hi] = a.id;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int j = tid; j < k; j += kMergeThreads) {
+        const bool ok = j < n && si[j] >= 0;
+        out_scores[(size_t)qi * k + j] = ok ? orderable_f32(ss[j]) : -INFINITY;
+        out_ids[(size_t)qi * k + j] = ok ? si[j] : -1;
+    }
+}
+
+}  // namespace
+
+int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st) {
+    search_begin_kernel<<<nq, 128, 0, st>>>(sc, q_dev, dim, want_split ? 1 : 0);
+    DAB_CUDA_OK(cudaGetLastError());
+    return DAB_OK;
+}
+
+int launch_compact(const SearchScratch &sc, int nq, int k_keep, int num_levels, cudaStream_t st) {
+    static bool attr_set = false;
+    const int smem = kCandCap * sizeof(uint64_t);
+    if (!attr_set) {
+        DAB_CUDA_OK(cudaFuncSetAttribute(compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    compact_kernel<<<nq, kCompactThreads, smem, st>>>(sc, nq, k_keep, num_levels);
+    DAB_CUDA_OK(cudaGetLastError());
+    return DAB_OK;
+}
+
+int launch_finish_exact(const SearchScratch &sc, const StoreView &sv, int nq, int k, int num_levels, float *out_scores,
+                        int64_t *out_ids, cudaStream_t st) {
+    finish_exact_kernel<<<nq, 128, 0, st>>>(sc, sv, k, num_levels, out_scores, out_ids);
+    DAB_CUDA_OK(cudaGetLastError());
+    return DAB_OK;
+}
+
+int launch_finish_rescore(const SearchScratch &sc, const StoreView &sv, int nq, int k, int k_keep, int num_levels,
+                          float *out_scores, int64_t *out_ids, cudaStream_t st) {
+    int P = 32;
+    while (P < k_keep) P <<= 1;
+    finish_rescore_kernel<<<nq, kRescoreThreads, P * sizeof(uint64_t), st>>>(sc, sv, k, k_keep, num_levels, out_scores, out_ids);
+    DAB_CUDA_OK(cudaGetLastError());
+    return DAB_OK;
+}
+
+int launch_fill_empty(float *out_scores, int64_t *out_ids, int64_t count, cudaStream_t st) {
+    if (count <= 0) return DAB_OK;
+    fill_empty_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(out_scores, out_ids, count);
+    DAB_CUDA_OK(cudaGetLastError());
+    return DAB_OK;
+}
+
+}  // namespace dab
+
+extern "C" DAB_API int dab_merge_topk(const float *gathered_scores, const int64_t *gathered_ids, int R, int Q, int k,
+                              float *out_scores, int64_t *out_ids, void *stream) {
+    using namespace dab;
+    if (!gathered_scores || !gathered_ids || !out_scores || !out_ids) return fail(DAB_E_INVALID, "dab_merge_topk: NULL pointer");
+    if (R <= 0 || Q < 0 || k <= 0) return fail(DAB_E_INVALID, "dab_merge_topk: R, k must be positive");
+    if ((long long)R * k > kMergeMax) return fail(DAB_E_CAPACITY, "dab_merge_topk: R*k exceeds 8192");
+    if (Q == 0) return DAB_OK;
+    int P = 32;
+    while (P < R * k) P <<= 1;
+    const int smem = P * (int)(sizeof(uint32_t) + sizeof(int64_t));
+    static bool attr_set = false;
+    if (!attr_set) {
+        DAB_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kMergeMax * (int)(sizeof(uint32_t) + sizeof(int64_t))));
+        attr_set = true;
+    }
+    merge_topk_kernel<<<Q, kMergeThreads, smem, static_cast<cudaStream_t>(stream)>>>(gathered_scores, gathered_ids, R, Q, k,
+                                                                                      out_scores, out_ids);
+    DAB_CUDA_OK(cudaGetLastError());
+    return DAB_OK;
+}

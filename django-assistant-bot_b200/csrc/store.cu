@@ -1,0 +1,338 @@
+// store.cu - the device-resident chunk-embedding store and the search orchestration.
+//
+// One dab_store is one shard of the table behind assistant/storage/models.py:19-29
+// (BaseEmbeddingModel.embedding) held in HBM: rows [capacity, dim] (fp32 like pgvector, or
+// bf16), 1/|row| per row, the row ids (Django pks), and the scratch a search needs.
+// dab_store_search is what `_objects_embedding_search` (assistant/rag/services/
+// search_service.py:185-196) becomes: exact cosine top-k, (score desc, row asc).
+#include <mutex>
+#include <new>
+
+#include "search.cuh"
+
+namespace dab {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string &msg) { g_last_error = msg; }
+int fail(int code, const std::string &msg) {
+    g_last_error = msg;
+    return code;
+}
+
+int simt_queries_per_pass(int dim, int dtype);
+void umma_release_maps(void *maps);
+
+}  // namespace dab
+
+struct dab_store {
+    int device = 0;
+    int dim = 0;
+    int dtype = DAB_F32;
+    int64_t capacity = 0;
+    int64_t size = 0;
+    int64_t id_base = 0;
+    bool explicit_ids = false;
+    void *rows = nullptr;
+    float *inv_norm = nullptr;
+    int64_t *ids = nullptr;
+    void *scratch_base = nullptr;
+    dab::SearchScratch scratch{};
+    int num_sms = 148;
+    int spare_rounds = 0;
+    int path = 0;
+    int last_num_levels = 0;
+    void *umma_maps = nullptr;  // tensor maps of the tcgen05 path (built lazily)
+    std::mutex mu;
+};
+
+namespace dab {
+
+namespace {
+
+// ---------------------------------------------------------------- append: copy/convert rows, 1/|row|
+// One warp per row; 128-bit loads/stores; the norm is taken from the values as STORED.
+template <bool IN_BF16, bool OUT_BF16>
+__global__ void __launch_bounds__(256)
+append_rows_kernel(const void *__restrict__ src, void *__restrict__ dst, float *__restrict__ inv_norm,
+                   int64_t *__restrict__ ids_dst, const int64_t *__restrict__ ids_src, int64_t id_first,
+                   int64_t n, int dim) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= n) return;
+    float ss = 0.f;
+    if constexpr (IN_BF16 && OUT_BF16) {
+        const uint4 *s = reinterpret_cast<const uint4 *>(static_cast<const __nv_bfloat16 *>(src) + row * dim);
+        uint4 *d = reinterpret_cast<uint4 *>(static_cast<__nv_bfloat16 *>(dst) + row * dim);
+        for (int c = lane; c < dim / 8; c += 32) {
+            const uint4 v = s[c];
+            d[c] = v;
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const float a = bf16_lo(w[i]), b = bf16_hi(w[i]);
+                ss = fmaf(a, a, ss);
+                ss = fmaf(b, b, ss);
+            }
+        }
+    } else if constexpr (!IN_BF16 && !OUT_BF16) {
+        const float4 *s = reinterpret_cast<const float4 *>(static_cast<const float *>(src) + row * dim);
+        float4 *d = reinterpret_cast<float4 *>(static_cast<float *>(dst) + row * dim);
+        for (int c = lane; c < dim / 4; c += 32) {
+            const float4 v = s[c];
+            d[c] = v;
+            ss = fmaf(v.x, v.x, ss);
+            ss = fmaf(v.y, v.y, ss);
+            ss = fmaf(v.z, v.z, ss);
+            ss = fmaf(v.w, v.w, ss);
+        }
+    } else if constexpr (!IN_BF16 && OUT_BF16) {
+        const float4 *s = reinterpret_cast<const float4 *>(static_cast<const float *>(src) + row * dim);
+        uint2 *d = reinterpret_cast<uint2 *>(static_cast<__nv_bfloat16 *>(dst) + row * dim);
+        for (int c = lane; c < dim / 4; c += 32) {
+            const float4 v = s[c];
+            const __nv_bfloat16 b0 = __float2bfloat16_rn(v.x), b1 = __float2bfloat16_rn(v.y);
+            const __nv_bfloat16 b2 = __float2bfloat16_rn(v.z), b3 = __float2bfloat16_rn(v.w);
+            uint2 o;
+            o.x = (uint32_t)__bfloat16_as_ushort(b0) | ((uint32_t)__bfloat16_as_ushort(b1) << 16);
+            o.y = (uint32_t)__bfloat16_as_ushort(b2) | ((uint32_t)__bfloat16_as_ushort(b3) << 16);
+            d[c] = o;
+            const float f0 = __bfloat162float(b0), f1 = __bfloat162float(b1), f2 = __bfloat162float(b2), f3 = __bfloat162float(b3);
+            ss = fmaf(f0, f0, ss);
+            ss = fmaf(f1, f1, ss);
+            ss = fmaf(f2, f2, ss);
+            ss = fmaf(f3, f3, ss);
+        }
+    }
+    ss = warp_sum(ss);
+    if (lane == 0) {
+        // NaN/inf rows get 0 as well: they can never be ranked (PostgreSQL sorts NaN distances last)
+        const float inv = (ss > 0.f && ss < INFINITY) ? 1.0f / sqrtf(ss) : 0.f;
+        inv_norm[row] = inv;
+        ids_dst[row] = ids_src ? ids_src[row] : id_first + row;
+    }
+}
+
+int check_store(const dab_store *s, const char *who) {
+    if (!s) return fail(DAB_E_INVALID, std::string(who) + ": store is NULL");
+    return DAB_OK;
+}
+
+}  // namespace
+}  // namespace dab
+
+using namespace dab;
+
+extern "C" DAB_API const char *dab_version(void) { return "dab_b200 0.1 sm_100a"; }
+extern "C" DAB_API const char *dab_last_error(void) { return g_last_error.c_str(); }
+
+extern "C" DAB_API int dab_store_create(dab_store **out, int device, int64_t capacity_rows, int dim, int dtype) {
+    if (!out) return fail(DAB_E_INVALID, "dab_store_create: out is NULL");
+    *out = nullptr;
+    if (dtype != DAB_F32 && dtype != DAB_BF16) return fail(DAB_E_INVALID, "dab_store_create: dtype must be DAB_F32 or DAB_BF16");
+    const int ve = dtype == DAB_BF16 ? 8 : 4;
+    if (dim <= 0 || dim % ve) return fail(DAB_E_INVALID, "dab_store_create: dim must be a positive multiple of 4 (fp32) / 8 (bf16)");
+    const size_t row_bytes = (size_t)dim * (dtype == DAB_BF16 ? 2 : 4);
+    if (row_bytes > DAB_MAX_ROW_BYTES) return fail(DAB_E_INVALID, "dab_store_create: row wider than DAB_MAX_ROW_BYTES");
+    if (capacity_rows <= 0 || capacity_rows >= (int64_t)0xffffffffll) return fail(DAB_E_INVALID, "dab_store_create: capacity must be in 1..2^32-2");
+    DAB_CUDA_OK(cudaSetDevice(device));
+    dab_store *s = new (std::nothrow) dab_store();
+    if (!s) return fail(DAB_E_INVALID, "dab_store_create: out of host memory");
+    s->device = device;
+    s->dim = dim;
+    s->dtype = dtype;
+    s->capacity = capacity_rows;
+    cudaError_t e;
+    auto bail = [&](const char *what, cudaError_t err) {
+        std::string m = std::string("dab_store_create: ") + what + ": " + cudaGetErrorString(err);
+        dab_store_destroy(s);
+        return fail(DAB_E_CUDA, m);
+    };
+    // tile reads may run past the last row by < one tile of inverse norms: pad
+    const size_t pad_rows = 256;
+    if ((e = cudaMalloc(&s->rows, (size_t)capacity_rows * row_bytes)) != cudaSuccess) return bail("rows", e);
+    if ((e = cudaMalloc(&s->inv_norm, ((size_t)capacity_rows + pad_rows) * sizeof(float))) != cudaSuccess) return bail("inv_norm", e);
+    if ((e = cudaMemset(s->inv_norm, 0, ((size_t)capacity_rows + pad_rows) * sizeof(float))) != cudaSuccess) return bail("memset", e);
+    if ((e = cudaMalloc(&s->ids, (size_t)capacity_rows * sizeof(int64_t))) != cudaSuccess) return bail("ids", e);
+    if ((e = cudaMalloc(&s->scratch_base, search_scratch_bytes(dim))) != cudaSuccess) return bail("scratch", e);
+    if ((e = cudaMemset(s->scratch_base, 0, search_scratch_bytes(dim))) != cudaSuccess) return bail("memset", e);
+    s->scratch = carve_scratch(s->scratch_base, dim);
+    int sms = 0;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bail("attr", e);
+    s->num_sms = sms;
+    *out = s;
+    return DAB_OK;
+}
+
+extern "C" DAB_API void dab_store_destroy(dab_store *s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->umma_maps) umma_release_maps(s->umma_maps);
+    cudaFree(s->rows);
+    cudaFree(s->inv_norm);
+    cudaFree(s->ids);
+    cudaFree(s->scratch_base);
+    delete s;
+}
+
+extern "C" DAB_API int64_t dab_store_size(const dab_store *s) { return s ? s->size : -1; }
+extern "C" DAB_API int64_t dab_store_capacity(const dab_store *s) { return s ? s->capacity : -1; }
+extern "C" DAB_API int dab_store_dim(const dab_store *s) { return s ? s->dim : -1; }
+extern "C" DAB_API int dab_store_dtype(const dab_store *s) { return s ? s->dtype : -1; }
+
+extern "C" DAB_API int dab_store_reset(dab_store *s) {
+    if (int rc = check_store(s, "dab_store_reset")) return rc;
+    std::lock_guard<std::mutex> g(s->mu);
+    s->size = 0;
+    s->explicit_ids = false;
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_set_id_base(dab_store *s, int64_t id_base) {
+    if (int rc = check_store(s, "dab_store_set_id_base")) return rc;
+    std::lock_guard<std::mutex> g(s->mu);
+    if (s->size) return fail(DAB_E_INVALID, "dab_store_set_id_base: store already holds rows");
+    s->id_base = id_base;
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds) {
+    if (int rc = check_store(s, "dab_store_set_spare_rounds")) return rc;
+    if (rounds < 0 || rounds > 64) return fail(DAB_E_INVALID, "dab_store_set_spare_rounds: 0..64");
+    std::lock_guard<std::mutex> g(s->mu);
+    s->spare_rounds = rounds;
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_set_path(dab_store *s, int path) {
+    if (int rc = check_store(s, "dab_store_set_path")) return rc;
+    if (path < 0 || path > 2) return fail(DAB_E_INVALID, "dab_store_set_path: 0 auto, 1 CUDA cores, 2 tcgen05");
+    if (path == 2 && !umma_supported(s->dim, s->dtype)) return fail(DAB_E_INVALID, "dab_store_set_path: tcgen05 path needs a bf16 store with dim % 64 == 0");
+    std::lock_guard<std::mutex> g(s->mu);
+    s->path = path;
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_append(dab_store *s, const void *rows_dev, int rows_dtype, const int64_t *ids_dev, int64_t n,
+                                void *stream) {
+    if (int rc = check_store(s, "dab_store_append")) return rc;
+    if (n < 0) return fail(DAB_E_INVALID, "dab_store_append: n < 0");
+    if (n == 0) return DAB_OK;
+    if (!rows_dev || !aligned16(rows_dev)) return fail(DAB_E_INVALID, "dab_store_append: rows must be a 16-byte aligned device pointer");
+    if (rows_dtype != DAB_F32 && rows_dtype != DAB_BF16) return fail(DAB_E_INVALID, "dab_store_append: rows_dtype must be DAB_F32 or DAB_BF16");
+    if (rows_dtype == DAB_BF16 && s->dtype == DAB_F32) return fail(DAB_E_INVALID, "dab_store_append: bf16 rows into an fp32 store are not widened; append fp32");
+    std::lock_guard<std::mutex> g(s->mu);
+    if (s->size + n > s->capacity) return fail(DAB_E_CAPACITY, "dab_store_append: store is full");
+    if (s->size > 0 && (ids_dev != nullptr) != s->explicit_ids)
+        return fail(DAB_E_INVALID, "dab_store_append: explicit and implicit ids cannot be mixed in one store");
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t row_bytes = (size_t)s->dim * (s->dtype == DAB_BF16 ? 2 : 4);
+    void *dst = static_cast<char *>(s->rows) + (size_t)s->size * row_bytes;
+    float *inv = s->inv_norm + s->size;
+    int64_t *idd = s->ids + s->size;
+    const int64_t id_first = s->id_base + s->size;
+    const unsigned blocks = (unsigned)((n + 7) / 8);
+    if (rows_dtype == DAB_BF16)
+        append_rows_kernel<true, true><<<blocks, 256, 0, st>>>(rows_dev, dst, inv, idd, ids_dev, id_first, n, s->dim);
+    else if (s->dtype == DAB_F32)
+        append_rows_kernel<false, false><<<blocks, 256, 0, st>>>(rows_dev, dst, inv, idd, ids_dev, id_first, n, s->dim);
+    else
+        append_rows_kernel<false, true><<<blocks, 256, 0, st>>>(rows_dev, dst, inv, idd, ids_dev, id_first, n, s->dim);
+    DAB_CUDA_OK(cudaGetLastError());
+    s->explicit_ids = ids_dev != nullptr;
+    s->size += n;
+    return DAB_OK;
+}
+
+namespace dab {
+
+// The rounds of one query chunk (<= 256 queries), all enqueued on `st` without a host sync.
+int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc, const float *q_dev, int nq, int k,
+                     const uint32_t *allow, float *out_scores, int64_t *out_ids, int *num_levels_out, cudaStream_t st) {
+    int path = s->path;
+    if (path == 0) path = (umma_supported(sv.dim, sv.dtype) && nq > simt_queries_per_pass(sv.dim, sv.dtype)) ? 2 : 1;
+    if (path == 2) {
+        // tensor path: hi+lo split of the query keeps the pass within ~1e-7 of fp32 while it is
+        // HBM-bound (2*nq <= 256 MMA columns); beyond that one bf16 pass plus a wider margin.
+        const bool split = 2 * nq <= DAB_MAX_QUERY_BATCH;
+        int k_keep = split ? k + 16 : 2 * k + 64;
+        if (k_keep > kCandCap / 4) k_keep = kCandCap / 4;
+        if (k_keep < k) k_keep = k;
+        const LevelPlan plan = make_level_plan(sv.n, umma_tile_rows(), k_keep);
+        *num_levels_out = plan.num_levels;
+        if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st)) return rc;
+        for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
+            if (int rc = launch_scan_umma(sv, allow, sc, nq, split, plan, s->num_sms, s->umma_maps, nullptr, st)) return rc;
+            if (int rc = launch_compact(sc, nq, k_keep, plan.num_levels, st)) return rc;
+        }
+        return launch_finish_rescore(sc, sv, nq, k, k_keep, plan.num_levels, out_scores, out_ids, st);
+    }
+    const int qb = simt_queries_per_pass(sv.dim, sv.dtype);
+    const LevelPlan plan = make_level_plan(sv.n, simt_tile_rows(sv.dim, sv.dtype), k);
+    *num_levels_out = plan.num_levels;
+    if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, false, st)) return rc;
+    for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
+        for (int q0 = 0; q0 < nq; q0 += qb) {
+            const int n_sub = nq - q0 < qb ? nq - q0 : qb;
+            if (int rc = launch_scan_simt(sv, allow, sc, q0, n_sub, plan, s->num_sms, st)) return rc;
+        }
+        if (int rc = launch_compact(sc, nq, k, plan.num_levels, st)) return rc;
+    }
+    return launch_finish_exact(sc, sv, nq, k, plan.num_levels, out_scores, out_ids, st);
+}
+
+int validate_search(const dab_store *s, const float *q_dev, int Q, int k, const float *out_scores, const int64_t *out_ids) {
+    if (!q_dev || !out_scores || !out_ids) return fail(DAB_E_INVALID, "dab_store_search: NULL pointer");
+    if (!aligned16(q_dev)) return fail(DAB_E_INVALID, "dab_store_search: queries must be 16-byte aligned");
+    if (Q < 0) return fail(DAB_E_INVALID, "dab_store_search: Q < 0");
+    if (k < 1 || k > DAB_MAX_K) return fail(DAB_E_INVALID, "dab_store_search: k must be in 1..DAB_MAX_K");
+    (void)s;
+    return DAB_OK;
+}
+
+}  // namespace dab
+
+extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow, float *out_scores,
+                                int64_t *out_ids, void *stream) {
+    if (int rc = check_store(s, "dab_store_search")) return rc;
+    if (int rc = validate_search(s, q_dev, Q, k, out_scores, out_ids)) return rc;
+    if (Q == 0) return DAB_OK;
+    std::lock_guard<std::mutex> g(s->mu);
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (s->size == 0) {
+        s->last_num_levels = 0;
+        return launch_fill_empty(out_scores, out_ids, (int64_t)Q * k, st);
+    }
+    StoreView sv;
+    sv.rows = s->rows;
+    sv.inv_norm = s->inv_norm;
+    sv.ids = s->explicit_ids ? s->ids : nullptr;
+    sv.id_base = s->id_base;
+    sv.n = s->size;
+    sv.dim = s->dim;
+    sv.dtype = s->dtype;
+    for (int q0 = 0; q0 < Q; q0 += DAB_MAX_QUERY_BATCH) {
+        const int nq = Q - q0 < DAB_MAX_QUERY_BATCH ? Q - q0 : DAB_MAX_QUERY_BATCH;
+        int levels = 0;
+        if (int rc = run_search_chunk(s, sv, s->scratch, q_dev + (size_t)q0 * s->dim, nq, k, allow,
+                                      out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, &levels, st))
+            return rc;
+        s->last_num_levels = levels;
+    }
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_search_status(dab_store *s, void *stream) {
+    if (int rc = check_store(s, "dab_store_search_status")) return rc;
+    std::lock_guard<std::mutex> g(s->mu);
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SearchCtrl c;
+    DAB_CUDA_OK(cudaMemcpyAsync(&c, s->scratch.ctrl, sizeof(c), cudaMemcpyDeviceToHost, st));
+    DAB_CUDA_OK(cudaStreamSynchronize(st));
+    if (s->last_num_levels > 0 && c.cur_level < s->last_num_levels)
+        return fail(DAB_E_INCOMPLETE, "search incomplete: candidate buffer overflowed " + std::to_string(c.overflow_events) +
+                                          " time(s); raise dab_store_set_spare_rounds and search again");
+    return DAB_OK;
+}

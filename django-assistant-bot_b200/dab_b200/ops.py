@@ -1,0 +1,216 @@
+"""Torch-facing wrappers over the C-ABI (tensors in, tensors out; torch only supplies device
+memory and streams).  Everything here requires CUDA tensors and raises otherwise."""
+from __future__ import annotations
+
+import threading
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import DabError, check, lib
+
+_DTYPES = {torch.float32: _lib.DAB_F32, torch.bfloat16: _lib.DAB_BF16}
+_MASK_DTYPES = {torch.uint8: _lib.DAB_MASK_U8, torch.bool: _lib.DAB_MASK_U8, torch.int32: _lib.DAB_MASK_I32,
+                torch.int64: _lib.DAB_MASK_I64}
+
+
+def _stream(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _need_cuda(t: torch.Tensor, what: str) -> None:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise DabError(_lib.DAB_E_INVALID, f"{what} must be a CUDA tensor (the B200 path has no CPU fallback)")
+
+
+def pool_l2norm(hidden: torch.Tensor, mask: Optional[torch.Tensor] = None, *, want_bf16: bool = False,
+                want_inv_norm: bool = False):
+    """Masked mean over tokens then L2 normalise: the batched form of
+    ``outputs.last_hidden_state.mean(dim=1)`` (assistant/ai/embedders/transformers.py:25).
+
+    hidden [B,T,D] fp32/bf16, mask [B,T] (bool/uint8/int32/int64; the HF attention_mask) or None.
+    Returns ``out`` [B,D] fp32, plus the bf16 copy and/or the applied 1/|mean| when asked.
+    """
+    _need_cuda(hidden, "hidden")
+    if hidden.dim() != 3:
+        raise DabError(_lib.DAB_E_INVALID, "hidden must be [B,T,D]")
+    if hidden.dtype not in _DTYPES:
+        raise DabError(_lib.DAB_E_INVALID, f"hidden dtype {hidden.dtype} unsupported (fp32 or bf16)")
+    hidden = hidden.contiguous()
+    B, T, D = hidden.shape
+    mptr, mdt = None, 0
+    if mask is not None:
+        _need_cuda(mask, "mask")
+        if tuple(mask.shape) != (B, T):
+            raise DabError(_lib.DAB_E_INVALID, f"mask shape {tuple(mask.shape)} != {(B, T)}")
+        if mask.dtype not in _MASK_DTYPES:
+            raise DabError(_lib.DAB_E_INVALID, f"mask dtype {mask.dtype} unsupported")
+        mask = mask.contiguous()
+        mptr, mdt = mask.data_ptr(), _MASK_DTYPES[mask.dtype]
+    dev = hidden.device
+    out = torch.empty((B, D), dtype=torch.float32, device=dev)
+    out_bf16 = torch.empty((B, D), dtype=torch.bfloat16, device=dev) if want_bf16 else None
+    out_inv = torch.empty((B,), dtype=torch.float32, device=dev) if want_inv_norm else None
+    with torch.cuda.device(dev):
+        check(lib().dab_pool_l2norm(hidden.data_ptr(), _DTYPES[hidden.dtype], mptr, mdt, out.data_ptr(),
+                                    out_bf16.data_ptr() if want_bf16 else None,
+                                    out_inv.data_ptr() if want_inv_norm else None, B, T, D, _stream(dev)))
+    res = (out,)
+    if want_bf16:
+        res += (out_bf16,)
+    if want_inv_norm:
+        res += (out_inv,)
+    return res[0] if len(res) == 1 else res
+
+
+def pack_allow_bitmap(allow: torch.Tensor) -> torch.Tensor:
+    """bool [n] row filter -> the uint32 bitmap dab_store_search takes (bit r of word r//32)."""
+    _need_cuda(allow, "allow")
+    a = allow.to(torch.bool).flatten()
+    n = a.numel()
+    words = (n + 31) // 32
+    pad = words * 32 - n
+    if pad:
+        a = torch.cat([a, torch.zeros(pad, dtype=torch.bool, device=a.device)])
+    w = (a.view(words, 32).to(torch.int64) << torch.arange(32, device=a.device, dtype=torch.int64)).sum(dim=1)
+    # same 32 bits, held in an int32 tensor (values >= 2^31 wrap to negative)
+    return (w - ((w >> 31) << 32)).to(torch.int32)
+
+
+class ChunkStore:
+    """One device-resident shard of the chunk-embedding table
+    (assistant/storage/models.py:19-29: ``embedding = VectorField(dimensions=768)``).
+
+    ``search`` is the device half of ``_objects_embedding_search``
+    (assistant/rag/services/search_service.py:185-196).
+    """
+
+    def __init__(self, capacity: int, dim: int, dtype: torch.dtype = torch.float32, device=None, id_base: int = 0):
+        if not torch.cuda.is_available():
+            raise DabError(_lib.DAB_E_CUDA, "no CUDA device: the B200 store has no CPU fallback")
+        if dtype not in _DTYPES:
+            raise DabError(_lib.DAB_E_INVALID, f"store dtype {dtype} unsupported (fp32 or bf16)")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.dim = int(dim)
+        self.dtype = dtype
+        self._h = _lib.c_void_p()
+        self._lock = threading.Lock()
+        check(lib().dab_store_create(_lib.ctypes.byref(self._h), self.device.index, int(capacity), int(dim), _DTYPES[dtype]))
+        if id_base:
+            check(lib().dab_store_set_id_base(self._h, int(id_base)))
+
+    # -- lifecycle
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().dab_store_destroy(self._h)
+            self._h = _lib.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __len__(self) -> int:
+        return int(lib().dab_store_size(self._h))
+
+    @property
+    def capacity(self) -> int:
+        return int(lib().dab_store_capacity(self._h))
+
+    def reset(self) -> None:
+        check(lib().dab_store_reset(self._h))
+
+    def set_path(self, path: str) -> None:
+        check(lib().dab_store_set_path(self._h, {"auto": 0, "simt": 1, "tcgen05": 2}[path]))
+
+    def set_spare_rounds(self, n: int) -> None:
+        check(lib().dab_store_set_spare_rounds(self._h, int(n)))
+
+    # -- write side
+    def append(self, rows: torch.Tensor, ids: Optional[torch.Tensor] = None) -> None:
+        _need_cuda(rows, "rows")
+        if rows.dim() != 2 or rows.shape[1] != self.dim:
+            raise DabError(_lib.DAB_E_DIM, f"different vector dimensions {rows.shape[-1]} and {self.dim}")
+        if rows.dtype not in _DTYPES:
+            raise DabError(_lib.DAB_E_INVALID, f"rows dtype {rows.dtype} unsupported")
+        rows = rows.contiguous()
+        iptr = None
+        if ids is not None:
+            _need_cuda(ids, "ids")
+            ids = ids.to(torch.int64).contiguous()
+            if ids.numel() != rows.shape[0]:
+                raise DabError(_lib.DAB_E_INVALID, "ids and rows disagree on the row count")
+            iptr = ids.data_ptr()
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_append(self._h, rows.data_ptr(), _DTYPES[rows.dtype], iptr, rows.shape[0],
+                                         _stream(self.device)))
+
+    # -- read side
+    def search_async(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None,
+                     out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
+        """Enqueue the search on the current stream; returns device tensors (scores [Q,k] fp32
+        descending, ids [Q,k] int64).  No host synchronisation.  See ``search`` for the checked form."""
+        _need_cuda(queries, "queries")
+        if queries.dim() == 1:
+            queries = queries[None, :]
+        if queries.shape[-1] != self.dim:
+            raise DabError(_lib.DAB_E_DIM, f"different vector dimensions {queries.shape[-1]} and {self.dim}")
+        queries = queries.to(torch.float32).contiguous()
+        Q = queries.shape[0]
+        if out is None:
+            scores = torch.empty((Q, k), dtype=torch.float32, device=self.device)
+            ids = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+        else:
+            scores, ids = out
+        aptr = None
+        if allow_bitmap is not None:
+            _need_cuda(allow_bitmap, "allow_bitmap")
+            if allow_bitmap.numel() * 32 < len(self):
+                raise DabError(_lib.DAB_E_INVALID, "allow bitmap shorter than the store")
+            aptr = allow_bitmap.data_ptr()
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_search(self._h, queries.data_ptr(), Q, int(k), aptr, scores.data_ptr(), ids.data_ptr(),
+                                         _stream(self.device)))
+        return scores, ids
+
+    def search(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None):
+        """Checked search: runs ``search_async``, waits, and if a scan round overflowed its
+        candidate buffer (adversarial row order) repeats with spare rounds until complete."""
+        with self._lock:
+            spare = 0
+            while True:
+                scores, ids = self.search_async(queries, k, allow_bitmap)
+                with torch.cuda.device(self.device):
+                    rc = lib().dab_store_search_status(self._h, _stream(self.device))
+                incomplete = rc == _lib.DAB_E_INCOMPLETE or bool(torch.isnan(scores).any())
+                if not incomplete:
+                    check(rc)
+                    if spare:
+                        self.set_spare_rounds(0)
+                    return scores, ids
+                spare = 4 if spare == 0 else spare * 2
+                if spare > 64:
+                    check(rc)
+                    raise DabError(_lib.DAB_E_INCOMPLETE, "search did not complete within 64 spare rounds")
+                self.set_spare_rounds(spare)
+
+
+def merge_topk(gathered_scores: torch.Tensor, gathered_ids: torch.Tensor):
+    """k-way merge of per-shard results: [R,Q,k] -> [Q,k] under (score desc, id asc)."""
+    _need_cuda(gathered_scores, "gathered_scores")
+    _need_cuda(gathered_ids, "gathered_ids")
+    if gathered_scores.dim() != 3 or gathered_scores.shape != gathered_ids.shape:
+        raise DabError(_lib.DAB_E_INVALID, "gathered tensors must both be [R,Q,k]")
+    gs = gathered_scores.to(torch.float32).contiguous()
+    gi = gathered_ids.to(torch.int64).contiguous()
+    R, Q, k = gs.shape
+    dev = gs.device
+    scores = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    ids = torch.empty((Q, k), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().dab_merge_topk(gs.data_ptr(), gi.data_ptr(), R, Q, k, scores.data_ptr(), ids.data_ptr(), _stream(dev)))
+    return scores, ids

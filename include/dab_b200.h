@@ -1,0 +1,152 @@
+/*
+ * dab_b200.h - C-ABI of the B200-native retrieval hot path for django-assistant-bot.
+ *
+ * This is the drop-in boundary: plain C types, device pointers and sizes, no torch
+ * types.  Each entry point names the reference interface it stands behind
+ * (paths relative to the reference repository root).  Shipped as libdab_b200.so
+ * (CUDA, sm_100a only).  There is no CPU fallback: every call needs a CUDA device.
+ *
+ * Conventions
+ *   - return 0 on success, a DAB_E_* code otherwise; dab_last_error() gives the
+ *     message for the calling thread.  Nothing aborts, nothing falls back to the CPU.
+ *   - all *_dev pointers are device pointers owned by the caller, 16-byte aligned,
+ *     contiguous (row-major).  `stream` is a cudaStream_t passed as void*; every call
+ *     is asynchronous with respect to it unless stated otherwise.
+ *   - the library owns only what dab_store_create allocates (rows, inverse norms, ids,
+ *     per-store scratch) and frees it in dab_store_destroy.
+ *   - thread safety: calls on different stores are independent; calls on one store are
+ *     serialised by a per-store mutex (the reference reaches this code from an asgiref
+ *     worker thread, assistant/rag/services/search_service.py:191, and from uvicorn
+ *     workers, gpu_service/gunicorn_conf.py:9).
+ */
+#ifndef DAB_B200_H
+#define DAB_B200_H
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define DAB_API __attribute__((visibility("default")))
+#else
+#define DAB_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dab_store dab_store;
+
+/* element types */
+#define DAB_F32 0
+#define DAB_BF16 1
+/* attention-mask element types (HF tokenizers emit int64) */
+#define DAB_MASK_U8 0
+#define DAB_MASK_I32 1
+#define DAB_MASK_I64 2
+
+/* error codes */
+#define DAB_OK 0
+#define DAB_E_INVALID 1     /* bad argument (null, misaligned, unsupported size) */
+#define DAB_E_CUDA 2        /* a CUDA runtime call failed */
+#define DAB_E_DIM 3         /* "different vector dimensions", like pgvector raises */
+#define DAB_E_CAPACITY 4    /* store full / size beyond a stated maximum */
+#define DAB_E_INCOMPLETE 5  /* a search did not finish its scan rounds (see dab_store_search_status) */
+
+/* limits */
+#define DAB_MAX_K 2048           /* largest n of a search; the reference uses 1, 5, 10, 250 */
+#define DAB_MAX_QUERY_BATCH 256  /* queries scored per corpus pass; larger Q is chunked */
+#define DAB_MAX_ROW_BYTES 8192   /* dim*sizeof(elem): 2048 fp32 / 4096 bf16 */
+
+/* Library version string, e.g. "dab_b200 0.1 sm_100a". */
+DAB_API const char *dab_version(void);
+
+/* Message of the last failing call on this thread (never NULL). */
+DAB_API const char *dab_last_error(void);
+
+/*
+ * Fused masked mean-pool + L2 normalise of encoder hidden states.
+ * Replaces: `outputs.last_hidden_state.mean(dim=1).squeeze().tolist()`
+ *           assistant/ai/embedders/transformers.py:25 (inside TransformersEmbedder.embeddings, :15-29),
+ *           generalised to a padded batch: e[b] = sum_t m[b,t] h[b,t,:] / max(sum_t m[b,t], 1),
+ *           out[b] = e[b] / max(|e[b]|, 1e-12).
+ *   hidden        [B,T,D] hidden_dtype (DAB_F32 | DAB_BF16)
+ *   mask          [B,T]   mask_dtype, non-zero = token counts; NULL = all tokens count
+ *   out           [B,D]   fp32, unit-norm rows (all-masked row -> zeros)
+ *   out_bf16      [B,D]   bf16 copy of `out` (RNE), or NULL
+ *   out_invnorm   [B]     the factor applied, 1/max(|e|,1e-12): out/out_invnorm is the
+ *                         reference's un-normalised mean; or NULL
+ * D must be a multiple of 4 (fp32) / 8 (bf16).
+ */
+DAB_API int dab_pool_l2norm(const void *hidden_dev, int hidden_dtype, const void *mask_dev, int mask_dtype,
+                    float *out_dev, void *out_bf16_dev_or_null, float *out_invnorm_dev_or_null,
+                    int64_t B, int64_t T, int64_t D, void *stream);
+
+/*
+ * Device-resident chunk-embedding store: one shard of the table behind
+ * assistant/storage/models.py:19-29 (BaseEmbeddingModel.embedding, vector(768) fp32, nullable)
+ * and :13 (Document.content_embedding).  Only non-NULL embeddings are stored.
+ *   dtype: DAB_F32 (what pgvector stores) or DAB_BF16.  Synchronous (allocates).
+ */
+DAB_API int dab_store_create(dab_store **out, int device, int64_t capacity_rows, int dim, int dtype);
+DAB_API void dab_store_destroy(dab_store *s);
+
+/* rows currently held / capacity / dim / dtype */
+DAB_API int64_t dab_store_size(const dab_store *s);
+DAB_API int64_t dab_store_capacity(const dab_store *s);
+DAB_API int dab_store_dim(const dab_store *s);
+DAB_API int dab_store_dtype(const dab_store *s);
+/* forget all rows (keeps the allocation) */
+DAB_API int dab_store_reset(dab_store *s);
+
+/*
+ * Append n rows.  Replaces the write side of the embedding column:
+ * `Sentence.objects.bulk_update(sentences, ['embedding'])`
+ * assistant/processing/documents/steps/embeddings.py:35-39,65-69.
+ *   rows_dev  [n,dim] rows_dtype (fp32 rows are rounded RNE into a bf16 store)
+ *   ids_dev   [n] int64 row ids (Django pks) or NULL = running row index (+ id_base)
+ * Also computes and keeps 1/|row| from the STORED values (0 for an all-zero row, which
+ * is then never returned - pgvector gives NaN distance for it and PostgreSQL sorts NaN last).
+ * Ties between equal scores are broken by store row order, i.e. by id when ids ascend
+ * with insertion order.
+ */
+DAB_API int dab_store_append(dab_store *s, const void *rows_dev, int rows_dtype, const int64_t *ids_dev_or_null,
+                     int64_t n, void *stream);
+/* id given to row i when ids are implicit: id_base + i (a shard's first global row index) */
+DAB_API int dab_store_set_id_base(dab_store *s, int64_t id_base);
+
+/*
+ * Exact cosine top-k of Q queries over the store.
+ * Replaces: `qs.annotate(distance=CosineDistance(field, q)).order_by('distance')[:n]`
+ *           assistant/rag/services/search_service.py:185-196 (_objects_embedding_search),
+ *           i.e. pgvector `<=>` + ORDER BY ... LIMIT n inside PostgreSQL.
+ *   q_dev        [Q,dim] fp32 queries (any norm)
+ *   k            n of the reference call, 1..DAB_MAX_K
+ *   allow_bitmap [ceil(size/32)] uint32, bit r set = row r passes the queryset filter; NULL = all
+ *   out_scores   [Q,k] fp32 cosine similarity, descending (distance = 1 - score)
+ *   out_ids      [Q,k] int64 row ids; (score desc, row order asc) ; unused slots: id -1, score -inf
+ * Asynchronous and sync-free: the scan rounds are enqueued optimistically.  If a round
+ * overflowed its candidate buffer more often than the spare rounds allow, the outputs are
+ * filled with id -1 / NaN and dab_store_search_status reports DAB_E_INCOMPLETE.
+ */
+DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
+                     float *out_scores_dev, int64_t *out_ids_dev, void *stream);
+/* Synchronises `stream`, returns DAB_OK or DAB_E_INCOMPLETE for the last search on `s`. */
+DAB_API int dab_store_search_status(dab_store *s, void *stream);
+/* extra scan rounds enqueued per search for overflow retries (default 0) */
+DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds);
+/* scoring path: 0 = auto, 1 = CUDA-core fp32 dot products, 2 = tcgen05 bf16 tensor tiles (bf16 stores) */
+DAB_API int dab_store_set_path(dab_store *s, int path);
+
+/*
+ * k-way merge of per-shard top-k lists (after the all-gather).  New in the build: the
+ * reference has a single PostgreSQL table; the sharded store needs the global ORDER BY.
+ *   gathered_scores [R,Q,k] fp32, gathered_ids [R,Q,k] int64 (id -1 = empty slot)
+ *   out_scores [Q,k], out_ids [Q,k]: (score desc, id asc).  R*k <= 8192.
+ */
+DAB_API int dab_merge_topk(const float *gathered_scores_dev, const int64_t *gathered_ids_dev, int R, int Q, int k,
+                   float *out_scores_dev, int64_t *out_ids_dev, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAB_B200_H */

@@ -1,0 +1,66 @@
+"""Parity of the fused pool+normalise CUDA kernel with the oracle (through the C-ABI)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pool_ref
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(hidden, mask, **kw):
+    from dab_b200 import ops
+    dev = torch.device("cuda:0")
+    return ops.pool_l2norm(hidden.to(dev), None if mask is None else mask.to(dev), **kw)
+
+
+def test_pool_matches_reference_golden(golden_dir):
+    """The CUDA kernel on the padded batch == the reference's per-text output, normalised
+    (assistant/ai/embedders/transformers.py:25), 1e-5 relative."""
+    g = np.load(os.path.join(golden_dir, "pool_ref.npz"))
+    out, inv = _run(torch.from_numpy(g["hidden"]), torch.from_numpy(g["mask"]), want_inv_norm=True)
+    ref = g["ref_embeddings"]
+    ref_unit = ref / np.linalg.norm(ref, axis=1, keepdims=True)
+    np.testing.assert_allclose(out.cpu().numpy(), ref_unit, rtol=1e-5, atol=2e-6)
+    # out / inv is the reference's raw (un-normalised) mean
+    np.testing.assert_allclose(out.cpu().numpy() / inv.cpu().numpy()[:, None], ref, rtol=2e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("B,T,D", [(32, 256, 384), (3, 7, 768), (5, 512, 1024), (2, 33, 2048), (1, 1, 8), (4, 19, 4096),
+                                   (300, 16, 64)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("mask_dtype", [torch.int64, torch.uint8, None])
+def test_pool_parity(B, T, D, dtype, mask_dtype):
+    g = torch.Generator().manual_seed(B * 1000 + T + D)
+    hidden = torch.randn(B, T, D, generator=g).to(dtype)
+    mask = None
+    if mask_dtype is not None:
+        lengths = torch.randint(1, T + 1, (B,), generator=g)
+        mask = (torch.arange(T)[None, :] < lengths[:, None]).to(mask_dtype)
+        if B > 1:
+            mask[1] = torch.randint(0, 2, (T,), generator=g).to(mask_dtype)  # ragged, non-prefix mask
+    out, ob, inv = _run(hidden, mask, want_bf16=True, want_inv_norm=True)
+    m = np.ones((B, T), dtype=np.int64) if mask is None else mask.numpy()
+    want, winv = pool_ref.masked_mean_pool(hidden.float().numpy(), m)
+    np.testing.assert_allclose(out.cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(inv.cpu().numpy(), winv, rtol=1e-5)
+    np.testing.assert_array_equal(ob.cpu().view(torch.int16).numpy(), out.cpu().to(torch.bfloat16).view(torch.int16).numpy())
+
+
+def test_pool_all_masked_row_and_empty_batch():
+    hidden = torch.randn(3, 9, 16)
+    mask = torch.ones(3, 9, dtype=torch.int64)
+    mask[1] = 0
+    out = _run(hidden, mask).cpu().numpy()
+    assert np.all(out[1] == 0) and np.isfinite(out).all()
+    assert _run(torch.zeros(0, 4, 16), None).shape == (0, 16)
+
+
+def test_pool_argument_errors():
+    from dab_b200 import DabError
+    with pytest.raises(DabError, match="multiple of 4"):
+        _run(torch.zeros(1, 2, 6), None)
+    with pytest.raises(DabError, match="mask shape"):
+        _run(torch.zeros(1, 2, 8), torch.ones(1, 3, dtype=torch.int64))
