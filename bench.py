@@ -1,0 +1,525 @@
+#!/usr/bin/env python
+"""bench.py - the headline measurement: exact cosine top-k queries/sec over the device store.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c4q64|c5] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic input: Q queries scored against
+the whole (sharded) corpus, local top-k, all-gather + k-way merge when N > 1.  Rank 0 prints ONE
+JSON line.  For N > 1 the driver launches this under torch.distributed.run (one rank per GPU, NCCL).
+
+  value      whole-job queries/sec with queries already resident in HBM (CUDA events, max over ranks)
+  e2e        the same through the public API with HOST buffers: pinned queries -> H2D -> checked
+             search (+ merge) -> D2H of scores/ids, every step
+  roofline   the scan kernel: algorithmic bytes (or flops) / its own event-timed duration, against
+             MEASURED_PEAKS.json
+  cpu_baseline  the oracle (oracle/scan_ref.c, pgvector `<=>` restatement, OpenMP over host cores) on a
+             bounded sample of the same workload, extrapolated linearly in rows - a reported
+             baseline, not the target
+`--impl reference` times that CPU restatement as the reference arm (the reference delegates this
+path to PostgreSQL+pgvector, unavailable on this box; kind "port").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "django-assistant-bot_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+# BASELINE.json configs (index 1..4); SURVEY.md section 8(d) shapes
+WORKLOADS = {
+    "c2": dict(kind="search", rows=1_000_000, dim=768, dtype="f32", Q=1, k=10,
+               desc="1M x 768 fp32 store, Q=1, top-10 (BASELINE.json configs[1])"),
+    "c3": dict(kind="search", rows=10_000_000, dim=1024, dtype="bf16", Q=64, k=100,
+               desc="10M x 1024 bf16 store, Q=64, top-100, exact fp32 rescoring (configs[2])"),
+    "c4": dict(kind="search", rows=100_000_000, dim=768, dtype="bf16", Q=256, k=100,
+               desc="100M x 768 bf16 store row-sharded over the GPUs, Q=256, top-100 (configs[3])"),
+    "c4q64": dict(kind="search", rows=100_000_000, dim=768, dtype="bf16", Q=64, k=100,
+                  desc="100M x 768 bf16 store row-sharded over the GPUs, Q=64, top-100 (north_star target)"),
+    "c5": dict(kind="pool", B=256, T=512, dim=1024, dtype="f32",
+               desc="ingest: masked mean-pool + L2 norm, 256 chunks x 512 tok x 1024-d fp32 per step per GPU (configs[4])"),
+}
+DEFAULT_WORKLOAD = "c2"
+BLOCK_ROWS = 1_000_000
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d["hbm_gbs"]), tf=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    tf_burst=float(d["bf16_tflops"]), source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tf=1400.0, tf_burst=1590.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def gen_block(torch, block_idx: int, rows: int, dim: int, device):
+    """Rows ~ N(0,1)^dim, L2-normalised in fp32; seed depends only on the GLOBAL block index, so
+    the corpus is the same however many GPUs it is sharded over."""
+    g = torch.Generator(device=device).manual_seed(1234 + block_idx)
+    x = torch.randn(rows, dim, generator=g, device=device, dtype=torch.float32)
+    return torch.nn.functional.normalize(x, dim=1)
+
+
+def gen_queries(torch, Q: int, dim: int):
+    g = torch.Generator().manual_seed(4321)
+    return torch.nn.functional.normalize(torch.randn(Q, dim, generator=g), dim=1)
+
+
+def cpu_search_sample(w, sample_rows_np, queries_np, budget_s: float, threads: int):
+    """Times oracle/scan_ref.c (vectorised build, OpenMP) on `sample_rows_np`; returns
+    (queries/sec extrapolated to the full row count, description)."""
+    from oracle import c_oracle
+    n_s = sample_rows_np.shape[0]
+    t0 = time.perf_counter()
+    c_oracle.search(sample_rows_np, queries_np[:1], w["k"], nthreads=threads)
+    t1 = time.perf_counter() - t0
+    nq = int(max(1, min(queries_np.shape[0], budget_s / max(t1, 1e-6))))
+    reps = 1 if nq > 1 else int(max(1, min(200, budget_s / max(t1, 1e-6))))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        c_oracle.search(sample_rows_np, queries_np[:nq], w["k"], nthreads=threads)
+    dt = (time.perf_counter() - t0) / (reps * nq)          # seconds per query on the sample
+    per_query_full = dt * (w["rows"] / n_s)
+    desc = (f"{nq} quer{'y' if nq == 1 else 'ies'} x {reps} rep(s) over the first {n_s} rows "
+            f"({per_query_full * 1e3:.1f} ms/query after linear extrapolation to {w['rows']} rows)")
+    return 1.0 / per_query_full, desc
+
+
+def run_reference_arm(args, w, rank, world):
+    """--impl reference: the CPU restatement of the path on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    import numpy as np
+    import torch
+    from oracle import c_oracle, search_ref
+    c_oracle.build()
+    threads = os.cpu_count() or 1
+    if w["kind"] == "pool":
+        from oracle import pool_ref
+        torch.manual_seed(777)
+        Bs = 32
+        hidden = torch.randn(Bs, w["T"], w["dim"])
+        lengths = torch.randint(16, w["T"] + 1, (Bs,), generator=torch.Generator().manual_seed(555))
+        mask = (torch.arange(w["T"])[None] < lengths[:, None]).long()
+        times = []
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            pool_ref.masked_mean_pool_torch_cpu(hidden, mask)
+            if i >= args.warmup:
+                times.append(time.perf_counter() - t0)
+        val = Bs / statistics.mean(times)
+        line = dict(metric="ingest pool+L2norm chunks/sec", value=val, unit="chunks/s", n_gpus=args.gpus, steps=args.steps,
+                    warmup=args.warmup, ms_per_step=1e3 * statistics.mean(times) * w["B"] / Bs, higher_is_better=True,
+                    scaling="weak", vs_baseline=None, dtype="f32", data="synthetic", impl="reference",
+                    config={"workload": args.workload, "desc": w["desc"]},
+                    cpu_baseline=dict(value=val, unit="chunks/s", cores=torch.get_num_threads(), kind="port",
+                                      sample=f"{Bs} chunks per step, CPU torch masked mean + F.normalize"),
+                    e2e=dict(value=val, unit="chunks/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+        print(json.dumps(line))
+        return
+    n_s = min(w["rows"], 250_000)
+    rng = np.random.default_rng(1234)
+    rows = rng.standard_normal((n_s, w["dim"]), dtype=np.float32)
+    rows /= np.linalg.norm(rows, axis=1, keepdims=True)
+    if w["dtype"] == "bf16":
+        rows = search_ref.f32_to_bf16_bits(rows)
+    q = gen_queries(torch, w["Q"], w["dim"]).numpy()
+    # one step = a bounded sample: up to 4 queries over n_s rows
+    nq = min(4, w["Q"])
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        c_oracle.search(rows, q[:nq], w["k"], nthreads=threads)
+        if i >= args.warmup:
+            times.append(time.perf_counter() - t0)
+    per_query_full = statistics.mean(times) / nq * (w["rows"] / n_s)
+    val = 1.0 / per_query_full
+    sample = (f"per step {nq} queries over a {n_s}-row sample; per-query time scaled linearly to {w['rows']} rows "
+              f"(pgvector scans one query at a time: Q queries = Q passes)")
+    line = dict(metric="exact cosine top-k queries/sec", value=val, unit="queries/s", n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=per_query_full * w["Q"] * 1e3, higher_is_better=True, scaling="strong",
+                vs_baseline=None, dtype="f32", data="synthetic", impl="reference",
+                config={"workload": args.workload, "desc": w["desc"], "rows": w["rows"], "dim": w["dim"],
+                        "store_dtype": w["dtype"], "Q": w["Q"], "k": w["k"]},
+                cpu_baseline=dict(value=val, unit="queries/s", cores=threads, kind="port", sample=sample),
+                e2e=dict(value=val, unit="queries/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("DAB_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override the corpus row count (debugging)")
+    ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-verify", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    w = dict(WORKLOADS[args.workload])
+    if args.rows:
+        w["rows"] = args.rows
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, w, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from dab_b200 import _lib, ops
+    peaks = load_peaks()
+    L = _lib.lib()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    if w["kind"] == "pool":
+        return bench_pool(args, w, rank, world, dev, peaks, barrier, max_over_ranks)
+
+    # ------------------------------------------------------------------ build the sharded store
+    N, D, Q, k = w["rows"], w["dim"], w["Q"], w["k"]
+    sdtype = torch.bfloat16 if w["dtype"] == "bf16" else torch.float32
+    lo, hi = rank * N // world, (rank + 1) * N // world          # contiguous row shard, ids = global row index
+    store = ops.ChunkStore(hi - lo, D, sdtype, dev, id_base=lo)
+    store.set_path(args.path)
+    sample_host = None
+    r = lo
+    while r < hi:
+        b = r // BLOCK_ROWS
+        b0 = b * BLOCK_ROWS
+        blk = gen_block(torch, b, min(BLOCK_ROWS, N - b0), D, dev)
+        part = blk[r - b0: min(hi, b0 + BLOCK_ROWS) - b0]
+        store.append(part)
+        if rank == 0 and sample_host is None and not args.no_cpu_baseline and world == 1:
+            s = part[:min(part.shape[0], 250_000)]
+            sample_host = (s.to(torch.bfloat16).view(torch.int16).cpu().numpy().view(np.uint16) if sdtype == torch.bfloat16
+                           else s.cpu().numpy())
+        r += part.shape[0]
+        del blk, part
+    torch.cuda.synchronize()
+    queries_host = gen_queries(torch, Q, D).pin_memory()
+    queries_dev = queries_host.to(dev)
+    out_host_s = torch.empty(Q, k, dtype=torch.float32).pin_memory()
+    out_host_i = torch.empty(Q, k, dtype=torch.int64).pin_memory()
+    gs = torch.empty(world, Q, k, dtype=torch.float32, device=dev) if world > 1 else None
+    gi = torch.empty(world, Q, k, dtype=torch.int64, device=dev) if world > 1 else None
+
+    def step_device():
+        s, i = store.search_async(queries_dev, k)
+        if world > 1:
+            dist.all_gather_into_tensor(gs, s)
+            dist.all_gather_into_tensor(gi, i)
+            s, i = ops.merge_topk(gs, gi)
+        return s, i
+
+    def step_e2e():
+        qd = queries_host.to(dev, non_blocking=True)
+        s, i = store.search(qd, k)                      # checked search: includes its own status sync
+        if world > 1:
+            dist.all_gather_into_tensor(gs, s)
+            dist.all_gather_into_tensor(gi, i)
+            s, i = ops.merge_topk(gs, gi)
+        out_host_s.copy_(s, non_blocking=True)
+        out_host_i.copy_(i, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            res = fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)), res
+
+    for _ in range(args.warmup):
+        step_device()
+    torch.cuda.synchronize()
+    status = L.dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
+    assert status == 0, f"warm-up search incomplete: {L.dab_last_error()}"
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = L.dab_launch_count()
+    ms_total, (res_s, res_i) = timed(step_device, args.steps)
+    launches = L.dab_launch_count() - launches0
+    status = L.dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
+    assert status == 0, f"timed search incomplete: {L.dab_last_error()}"
+    ms_e2e, _ = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # roofline pass: the scan kernel bracketed by events on its own stream
+    store.set_profile(True)
+    barrier()
+    for _ in range(args.steps):
+        step_device()
+    prof = store.get_profile()
+    store.set_profile(False)
+    scan_ms = max_over_ranks(prof["scan_ms"]) / args.steps            # per search, slowest rank
+    search_ms = max_over_ranks(prof["search_ms"]) / args.steps
+    elem = 2 if w["dtype"] == "bf16" else 4
+    n_local = hi - lo
+    alg_bytes = n_local * (D * elem + 4) + Q * D * 4 + Q * k * 12       # SURVEY 8(d), per GPU per query batch
+    alg_flops = 2.0 * Q * n_local * D
+    t_hbm, t_tf = alg_bytes / (peaks["hbm"] * 1e9), alg_flops / (peaks["tf"] * 1e12)
+    if t_tf > t_hbm and w["dtype"] == "bf16":
+        roof = dict(bound="tensor", achieved=alg_flops / (scan_ms * 1e-3) / 1e12, peak=peaks["tf"], unit="TFLOP/s")
+        roof["hbm_frac"] = alg_bytes / (scan_ms * 1e-3) / 1e9 / peaks["hbm"]
+    else:
+        roof = dict(bound="hbm", achieved=alg_bytes / (scan_ms * 1e-3) / 1e9, peak=peaks["hbm"], unit="GB/s")
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    roof["kernel"] = "scan (all level launches of one search)"
+    roof["scan_ms_per_search"] = scan_ms
+    roof["search_ms_per_search"] = search_ms
+    roof["scan_launches_per_search"] = prof["scan_launches"] / max(1, args.steps)
+    roof["peak_source"] = peaks["source"]
+    roof["traffic"] = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        roof["traffic"] = json.load(open(tpath)).get(args.workload)
+
+    # correctness guard: device fp32 oracle on a few queries over the whole shard (not timed)
+    verified = None
+    if not args.no_verify:
+        verified = verify(torch, ops, store, res_s, res_i, queries_dev, w, lo, hi, N, dev, world, dist)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    value = Q * args.steps / (ms_total * 1e-3)
+    e2e_val = Q * args.steps / (ms_e2e * 1e-3)
+    line = dict(metric="exact cosine top-k queries/sec", value=value, unit="queries/s", n_gpus=world, steps=args.steps,
+                warmup=args.warmup, ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="strong",
+                vs_baseline=None, dtype="f32", data="synthetic",
+                config={"workload": args.workload, "desc": w["desc"], "rows": N, "rows_per_gpu": n_local, "dim": D,
+                        "store_dtype": w["dtype"], "Q": Q, "k": k, "path": args.path,
+                        "l2": "inputs larger than L2: every step streams the whole shard "
+                              f"({n_local * D * elem / 1e9:.2f} GB >> 126 MB L2)"},
+                e2e=dict(value=e2e_val, unit="queries/s", h2d_bytes_per_step=Q * D * 4, d2h_bytes_per_step=Q * k * 12,
+                         ms_per_step=ms_e2e / args.steps),
+                gpu_launches=int(launches), clocks=clocks, roofline=roof, verified=verified)
+    if world == 1 and not args.no_cpu_baseline and sample_host is not None:
+        from oracle import c_oracle
+        c_oracle.build()
+        threads = os.cpu_count() or 1
+        v, desc = cpu_search_sample(w, sample_host, queries_host.numpy(), 12.0, threads)
+        line["cpu_baseline"] = dict(value=v, unit="queries/s", cores=threads, kind="port", sample=desc)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def verify(torch, ops, store, res_s, res_i, queries_dev, w, lo, hi, N, dev, world, dist):
+    """Regenerates the shard block by block and ranks the first queries with a plain fp32 torch
+    matmul (TF32 off); the bench's last result must match under the parity bar."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    nq = min(4, w["Q"])
+    k = w["k"]
+    q = queries_dev[:nq]
+    sdtype = torch.bfloat16 if w["dtype"] == "bf16" else torch.float32
+    best_s = torch.full((nq, k), float("-inf"), device=dev)
+    best_i = torch.full((nq, k), -1, dtype=torch.int64, device=dev)
+    r = lo
+    while r < hi:
+        b = r // BLOCK_ROWS
+        b0 = b * BLOCK_ROWS
+        blk = gen_block(torch, b, min(BLOCK_ROWS, N - b0), w["dim"], dev)
+        part = blk[r - b0: min(hi, b0 + BLOCK_ROWS) - b0].to(sdtype).float()
+        sc = (q @ part.T) / part.norm(dim=1)[None, :]
+        ids = torch.arange(r, r + part.shape[0], device=dev)[None, :].expand(nq, -1)
+        cs, ci = torch.cat([best_s, sc], 1), torch.cat([best_i, ids], 1)
+        top = torch.topk(cs, k, dim=1)
+        best_s, best_i = top.values, torch.gather(ci, 1, top.indices)
+        r += part.shape[0]
+    if world > 1:
+        gs = torch.empty(world, nq, k, device=dev)
+        gi = torch.empty(world, nq, k, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(gs, best_s.contiguous())
+        dist.all_gather_into_tensor(gi, best_i.contiguous())
+        cs, ci = gs.permute(1, 0, 2).reshape(nq, -1), gi.permute(1, 0, 2).reshape(nq, -1)
+        top = torch.topk(cs, k, dim=1)
+        best_s, best_i = top.values, torch.gather(ci, 1, top.indices)
+    got_s, got_i = res_s[:nq], res_i[:nq]
+    bad = 0
+    for qi in range(nq):
+        for j in range(k):
+            if got_i[qi, j] != best_i[qi, j]:
+                # allowed only for near-ties (< 1e-6)
+                alt = (best_i[qi] == got_i[qi, j]).nonzero()
+                other = float(best_s[qi, alt[0, 0]]) if alt.numel() else float(got_s[qi, j])
+                if abs(other - float(best_s[qi, j])) >= 1e-6:
+                    bad += 1
+        if not torch.allclose(got_s[qi], best_s[qi], rtol=1e-5, atol=1e-5):
+            bad += 1
+    assert bad == 0, f"bench result disagrees with the device fp32 oracle in {bad} place(s)"
+    return f"top-{k} of {nq} queries identical to a torch fp32 matmul ranking over all {N} rows"
+
+
+def bench_pool(args, w, rank, world, dev, peaks, barrier, max_over_ranks):
+    import torch
+    import torch.distributed as dist
+    from dab_b200 import _lib, ops
+    L = _lib.lib()
+    B, T, D = w["B"], w["T"], w["dim"]
+    g = torch.Generator(device=dev).manual_seed(777 + rank)
+    # several resident batches so that consecutive steps never re-read L2-resident data
+    nb = 4
+    hidden = [torch.randn(B, T, D, generator=g, device=dev) for _ in range(nb)]
+    lengths = torch.randint(16, T + 1, (B,), generator=torch.Generator().manual_seed(555))
+    mask = (torch.arange(T)[None] < lengths[:, None]).to(torch.int64)
+    mask_dev = mask.to(dev)
+    hidden_host = torch.randn(B, T, D).pin_memory()
+    mask_host = mask.pin_memory()
+    out_host = torch.empty(B, D).pin_memory()
+    it = [0]
+
+    def step_device():
+        it[0] += 1
+        return ops.pool_l2norm(hidden[it[0] % nb], mask_dev)
+
+    def step_e2e():
+        h = hidden_host.to(dev, non_blocking=True)
+        m = mask_host.to(dev, non_blocking=True)
+        out_host.copy_(ops.pool_l2norm(h, m), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1))
+
+    for _ in range(args.warmup):
+        step_device()
+    sampler = ClockSampler(dev.index)
+    if rank == 0:
+        sampler.start()
+    l0 = L.dab_launch_count()
+    ms = timed(step_device, args.steps)
+    launches = L.dab_launch_count() - l0
+    ms_e2e = timed(step_e2e, max(3, args.steps // 4))
+    e2e_steps = max(3, args.steps // 4)
+    clocks = sampler.stop() if rank == 0 else None
+    # the kernel skips masked-out token rows, so the bytes it must move are the unmasked ones
+    tokens = int(mask.sum())
+    alg_bytes = tokens * D * 4 + B * T * 8 + B * D * 4
+    nominal_bytes = B * (T * D * 4 + T * 8 + D * 4)
+    ach = alg_bytes / (ms / args.steps * 1e-3) / 1e9
+    if rank != 0:
+        return
+    line = dict(metric="ingest pool+L2norm chunks/sec", value=world * B * args.steps / (ms * 1e-3), unit="chunks/s",
+                n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True,
+                scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+                config={"workload": args.workload, "desc": w["desc"], "B": B, "T": T, "dim": D,
+                        "l2": f"{nb} resident batches of {B * T * D * 4 / 1e6:.0f} MB rotated (> 126 MB L2)"},
+                e2e=dict(value=world * B * e2e_steps / (ms_e2e * 1e-3), unit="chunks/s",
+                         h2d_bytes_per_step=B * T * D * 4 + B * T * 8, d2h_bytes_per_step=B * D * 4),
+                gpu_launches=int(launches), clocks=clocks,
+                roofline=dict(bound="hbm", achieved=ach, peak=peaks["hbm"], unit="GB/s", frac=ach / peaks["hbm"],
+                              traffic=None, kernel="pool_l2norm_kernel", peak_source=peaks["source"],
+                              note=f"algorithmic bytes count only unmasked token rows ({tokens} of {B * T}); "
+                                   f"with every row counted: {nominal_bytes / (ms / args.steps * 1e-3) / 1e9:.0f} GB/s"))
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import pool_ref
+        hs, msk = hidden_host[:32], mask[:32]
+        t0 = time.perf_counter()
+        reps = 0
+        while time.perf_counter() - t0 < 10.0:
+            pool_ref.masked_mean_pool_torch_cpu(hs, msk)
+            reps += 1
+        dt = (time.perf_counter() - t0) / reps
+        line["cpu_baseline"] = dict(value=32 / dt, unit="chunks/s", cores=torch.get_num_threads(), kind="port",
+                                    sample=f"{reps} reps of 32 chunks, CPU torch masked mean + F.normalize")
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

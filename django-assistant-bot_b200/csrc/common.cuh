@@ -24,6 +24,14 @@ int fail(int code, const std::string &msg);
             return ::dab::fail(DAB_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
     } while (0)
 
+// every kernel launch of the library is counted (bench.py reports it as gpu_launches)
+void count_launch();
+#define DAB_LAUNCH_OK()                      \
+    do {                                     \
+        ::dab::count_launch();               \
+        DAB_CUDA_OK(cudaGetLastError());     \
+    } while (0)
+
 static inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // ---------------------------------------------------------------- candidate keys

@@ -213,6 +213,7 @@ int launch_pool(const void *hidden, const void *mask, int mask_dtype, float *out
     DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, static_cast<const uint4 *>(hidden), mask, mask_dtype, out,
                                    static_cast<__nv_bfloat16 *>(out_bf16), out_inv, (int)T, (int)D, vecs_per_row,
                                    row_groups));
+    count_launch();
     return DAB_OK;
 }
 
@@ -230,11 +231,11 @@ int pool_pick_splits(int64_t B, int64_t T, int row_groups) {
 extern "C" DAB_API int dab_pool_l2norm(const void *hidden, int hidden_dtype, const void *mask, int mask_dtype, float *out,
                                void *out_bf16, float *out_inv, int64_t B, int64_t T, int64_t D, void *stream) {
     using namespace dab;
-    if (!hidden || !out) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden/out must not be NULL");
+    if (B == 0 && T >= 0 && D > 0) return DAB_OK;
+    if (!out || (!hidden && T > 0)) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden/out must not be NULL");
     if (hidden_dtype != DAB_F32 && hidden_dtype != DAB_BF16) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden_dtype must be DAB_F32 or DAB_BF16");
     if (mask && (mask_dtype < DAB_MASK_U8 || mask_dtype > DAB_MASK_I64)) return fail(DAB_E_INVALID, "dab_pool_l2norm: bad mask_dtype");
     if (B < 0 || T < 0 || D <= 0) return fail(DAB_E_INVALID, "dab_pool_l2norm: negative size");
-    if (B == 0) return DAB_OK;
     if (B > 65535) return fail(DAB_E_INVALID, "dab_pool_l2norm: B > 65535, split the batch");
     if (T > (1 << 24)) return fail(DAB_E_INVALID, "dab_pool_l2norm: T too large");
     const int ve = hidden_dtype == DAB_BF16 ? 8 : 4;

@@ -192,7 +192,7 @@ int launch_one(const StoreView &sv, const uint32_t *allow, const SearchScratch &
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
     kern<<<grid, kScanThreads, smem, st>>>(sv, allow, sc, q0, nq, plan);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     return DAB_OK;
 }
 

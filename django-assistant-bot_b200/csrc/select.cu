@@ -384,7 +384,7 @@ merge_topk_kernel(const float *__restrict__ gs, const int64_t *__restrict__ gi, 
 
 int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st) {
     search_begin_kernel<<<nq, 128, 0, st>>>(sc, q_dev, dim, want_split ? 1 : 0);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     return DAB_OK;
 }
 
@@ -396,14 +396,14 @@ int launch_compact(const SearchScratch &sc, int nq, int k_keep, int num_levels, 
         attr_set = true;
     }
     compact_kernel<<<nq, kCompactThreads, smem, st>>>(sc, nq, k_keep, num_levels);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     return DAB_OK;
 }
 
 int launch_finish_exact(const SearchScratch &sc, const StoreView &sv, int nq, int k, int num_levels, float *out_scores,
                         int64_t *out_ids, cudaStream_t st) {
     finish_exact_kernel<<<nq, 128, 0, st>>>(sc, sv, k, num_levels, out_scores, out_ids);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     return DAB_OK;
 }
 
@@ -412,14 +412,14 @@ int launch_finish_rescore(const SearchScratch &sc, const StoreView &sv, int nq, 
     int P = 32;
     while (P < k_keep) P <<= 1;
     finish_rescore_kernel<<<nq, kRescoreThreads, P * sizeof(uint64_t), st>>>(sc, sv, k, k_keep, num_levels, out_scores, out_ids);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     return DAB_OK;
 }
 
 int launch_fill_empty(float *out_scores, int64_t *out_ids, int64_t count, cudaStream_t st) {
     if (count <= 0) return DAB_OK;
     fill_empty_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(out_scores, out_ids, count);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     return DAB_OK;
 }
 
@@ -443,6 +443,6 @@ extern "C" DAB_API int dab_merge_topk(const float *gathered_scores, const int64_
     }
     merge_topk_kernel<<<Q, kMergeThreads, smem, static_cast<cudaStream_t>(stream)>>>(gathered_scores, gathered_ids, R, Q, k,
                                                                                       out_scores, out_ids);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     return DAB_OK;
 }

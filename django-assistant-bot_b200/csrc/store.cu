@@ -5,8 +5,11 @@
 // bf16), 1/|row| per row, the row ids (Django pks), and the scratch a search needs.
 // dab_store_search is what `_objects_embedding_search` (assistant/rag/services/
 // search_service.py:185-196) becomes: exact cosine top-k, (score desc, row asc).
+#include <atomic>
 #include <mutex>
 #include <new>
+#include <utility>
+#include <vector>
 
 #include "search.cuh"
 
@@ -19,10 +22,20 @@ int fail(int code, const std::string &msg) {
     return code;
 }
 
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
 int simt_queries_per_pass(int dim, int dtype);
 void umma_release_maps(void *maps);
 
 }  // namespace dab
+
+// cudaEvent pairs around the scan launches of a search (only when profiling is switched on)
+struct dab_profile {
+    bool on = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> scan_events;  // per scan launch
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> search_events;  // per search call
+};
 
 struct dab_store {
     int device = 0;
@@ -42,6 +55,7 @@ struct dab_store {
     int path = 0;
     int last_num_levels = 0;
     void *umma_maps = nullptr;  // tensor maps of the tcgen05 path (built lazily)
+    dab_profile prof;
     std::mutex mu;
 };
 
@@ -238,13 +252,32 @@ extern "C" DAB_API int dab_store_append(dab_store *s, const void *rows_dev, int 
         append_rows_kernel<false, false><<<blocks, 256, 0, st>>>(rows_dev, dst, inv, idd, ids_dev, id_first, n, s->dim);
     else
         append_rows_kernel<false, true><<<blocks, 256, 0, st>>>(rows_dev, dst, inv, idd, ids_dev, id_first, n, s->dim);
-    DAB_CUDA_OK(cudaGetLastError());
+    DAB_LAUNCH_OK();
     s->explicit_ids = ids_dev != nullptr;
     s->size += n;
     return DAB_OK;
 }
 
 namespace dab {
+
+// Brackets one kernel launch with cudaEvents on its own stream when profiling is on.
+struct ScanTimer {
+    dab_profile &p;
+    cudaStream_t st;
+    cudaEvent_t a = nullptr, b = nullptr;
+    ScanTimer(dab_profile &p_, cudaStream_t st_, bool whole_search = false) : p(p_), st(st_), whole(whole_search) {
+        if (!p.on) return;
+        if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) { a = b = nullptr; return; }
+        cudaEventRecord(a, st);
+    }
+    void stop() {
+        if (!a) return;
+        cudaEventRecord(b, st);
+        (whole ? p.search_events : p.scan_events).emplace_back(a, b);
+        a = b = nullptr;
+    }
+    bool whole;
+};
 
 // The rounds of one query chunk (<= 256 queries), all enqueued on `st` without a host sync.
 int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc, const float *q_dev, int nq, int k,
@@ -262,7 +295,9 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
         *num_levels_out = plan.num_levels;
         if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st)) return rc;
         for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
+            ScanTimer tm(s->prof, st);
             if (int rc = launch_scan_umma(sv, allow, sc, nq, split, plan, s->num_sms, s->umma_maps, nullptr, st)) return rc;
+            tm.stop();
             if (int rc = launch_compact(sc, nq, k_keep, plan.num_levels, st)) return rc;
         }
         return launch_finish_rescore(sc, sv, nq, k, k_keep, plan.num_levels, out_scores, out_ids, st);
@@ -274,7 +309,9 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
     for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
         for (int q0 = 0; q0 < nq; q0 += qb) {
             const int n_sub = nq - q0 < qb ? nq - q0 : qb;
+            ScanTimer tm(s->prof, st);
             if (int rc = launch_scan_simt(sv, allow, sc, q0, n_sub, plan, s->num_sms, st)) return rc;
+            tm.stop();
         }
         if (int rc = launch_compact(sc, nq, k, plan.num_levels, st)) return rc;
     }
@@ -282,10 +319,11 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
 }
 
 int validate_search(const dab_store *s, const float *q_dev, int Q, int k, const float *out_scores, const int64_t *out_ids) {
-    if (!q_dev || !out_scores || !out_ids) return fail(DAB_E_INVALID, "dab_store_search: NULL pointer");
-    if (!aligned16(q_dev)) return fail(DAB_E_INVALID, "dab_store_search: queries must be 16-byte aligned");
     if (Q < 0) return fail(DAB_E_INVALID, "dab_store_search: Q < 0");
     if (k < 1 || k > DAB_MAX_K) return fail(DAB_E_INVALID, "dab_store_search: k must be in 1..DAB_MAX_K");
+    if (Q == 0) return DAB_OK;
+    if (!q_dev || !out_scores || !out_ids) return fail(DAB_E_INVALID, "dab_store_search: NULL pointer");
+    if (!aligned16(q_dev)) return fail(DAB_E_INVALID, "dab_store_search: queries must be 16-byte aligned");
     (void)s;
     return DAB_OK;
 }
@@ -312,6 +350,11 @@ extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q,
     sv.n = s->size;
     sv.dim = s->dim;
     sv.dtype = s->dtype;
+    ScanTimer whole(s->prof, st, true);
+    struct Stop {
+        ScanTimer &t;
+        ~Stop() { t.stop(); }
+    } stop_on_exit{whole};
     for (int q0 = 0; q0 < Q; q0 += DAB_MAX_QUERY_BATCH) {
         const int nq = Q - q0 < DAB_MAX_QUERY_BATCH ? Q - q0 : DAB_MAX_QUERY_BATCH;
         int levels = 0;
@@ -334,5 +377,37 @@ extern "C" DAB_API int dab_store_search_status(dab_store *s, void *stream) {
     if (s->last_num_levels > 0 && c.cur_level < s->last_num_levels)
         return fail(DAB_E_INCOMPLETE, "search incomplete: candidate buffer overflowed " + std::to_string(c.overflow_events) +
                                           " time(s); raise dab_store_set_spare_rounds and search again");
+    return DAB_OK;
+}
+
+extern "C" DAB_API uint64_t dab_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+extern "C" DAB_API int dab_store_set_profile(dab_store *s, int on) {
+    if (int rc = check_store(s, "dab_store_set_profile")) return rc;
+    std::lock_guard<std::mutex> g(s->mu);
+    s->prof.on = on != 0;
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_get_profile(dab_store *s, float *scan_ms, int *scan_launches, float *search_ms,
+                                             int *searches) {
+    if (int rc = check_store(s, "dab_store_get_profile")) return rc;
+    std::lock_guard<std::mutex> g(s->mu);
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    DAB_CUDA_OK(cudaDeviceSynchronize());
+    auto drain = [](std::vector<std::pair<cudaEvent_t, cudaEvent_t>> &v, float *ms, int *n) {
+        float tot = 0.f;
+        for (auto &e : v) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, e.first, e.second) == cudaSuccess) tot += t;
+            cudaEventDestroy(e.first);
+            cudaEventDestroy(e.second);
+        }
+        if (ms) *ms = tot;
+        if (n) *n = (int)v.size();
+        v.clear();
+    };
+    drain(s->prof.scan_events, scan_ms, scan_launches);
+    drain(s->prof.search_events, search_ms, searches);
     return DAB_OK;
 }

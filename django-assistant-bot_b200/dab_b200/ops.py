@@ -130,6 +130,17 @@ class ChunkStore:
     def set_spare_rounds(self, n: int) -> None:
         check(lib().dab_store_set_spare_rounds(self._h, int(n)))
 
+    def set_profile(self, on: bool) -> None:
+        check(lib().dab_store_set_profile(self._h, 1 if on else 0))
+
+    def get_profile(self) -> dict:
+        """Summed cudaEvent times since the last call: scan kernels and whole searches (ms)."""
+        sm, sn = _lib.ctypes.c_float(), _lib.c_int()
+        tm, tn = _lib.ctypes.c_float(), _lib.c_int()
+        check(lib().dab_store_get_profile(self._h, _lib.ctypes.byref(sm), _lib.ctypes.byref(sn), _lib.ctypes.byref(tm),
+                                          _lib.ctypes.byref(tn)))
+        return {"scan_ms": sm.value, "scan_launches": sn.value, "search_ms": tm.value, "searches": tn.value}
+
     # -- write side
     def append(self, rows: torch.Tensor, ids: Optional[torch.Tensor] = None) -> None:
         _need_cuda(rows, "rows")

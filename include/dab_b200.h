@@ -146,6 +146,19 @@ DAB_API int dab_store_set_path(dab_store *s, int path);
 DAB_API int dab_merge_topk(const float *gathered_scores_dev, const int64_t *gathered_ids_dev, int R, int Q, int k,
                    float *out_scores_dev, int64_t *out_ids_dev, void *stream);
 
+/*
+ * Measurement hooks (no counterpart in the reference, which only has the wall-clock
+ * TimeDebugger of assistant/utils/debug.py:5-30 around the whole search).
+ *   dab_launch_count      kernels this library has launched in this process
+ *   dab_store_set_profile on: every scan launch and every search call is bracketed by
+ *                         cudaEvents on the caller's stream
+ *   dab_store_get_profile synchronises the device, returns the summed event times since the
+ *                         last call and clears them
+ */
+DAB_API uint64_t dab_launch_count(void);
+DAB_API int dab_store_set_profile(dab_store *s, int on);
+DAB_API int dab_store_get_profile(dab_store *s, float *scan_ms, int *scan_launches, float *search_ms, int *searches);
+
 #ifdef __cplusplus
 }
 #endif
