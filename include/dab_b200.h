@@ -147,6 +147,38 @@ DAB_API int dab_merge_topk(const float *gathered_scores_dev, const int64_t *gath
                    float *out_scores_dev, int64_t *out_ids_dev, void *stream);
 
 /*
+ * Exact cosine top-k over rows the CALLER owns, without allocating anything.
+ * No counterpart in the reference (there the rows live in PostgreSQL and the executor
+ * allocates as it pleases); it exists for hosts of this library that cannot call cudaMalloc:
+ * code running inside the embedding service after the encoder's allocator has reserved the
+ * GPU, request handlers that cannot afford cudaMalloc's device-wide synchronisation, and
+ * callers ranking embeddings they keep in their own buffers.  Same result as
+ * dab_store_append + dab_store_search on the same rows (CUDA-core fp32 path).
+ *   rows_dev      [n_rows, dim] DAB_F32 or DAB_BF16, 16-byte aligned
+ *   inv_norm_dev  [n_rows] fp32, 1/|row| (0 = never return this row); must be readable up to
+ *                 n_rows rounded up to a multiple of 4
+ *   id_base       ids written are id_base + row index
+ *   q_dev, k, allow_bitmap, out_scores_dev, out_ids_dev: as dab_store_search
+ * The scratch a search needs (unit queries, 8192 candidate keys per query, thresholds, round
+ * control) lives in one static __device__ array of DAB_NOALLOC_SCRATCH_BYTES that every GPU
+ * loading the library holds until exit.  Hence the limits: Q <= DAB_NOALLOC_MAX_QUERIES,
+ * dim <= DAB_NOALLOC_MAX_DIM, else DAB_E_CAPACITY.  All calls on a device share that array:
+ * each call resets the state it reads, but calls that overlap on the GPU (two streams) race -
+ * keep them on one stream or order them with events.  The first call on a device resolves the
+ * array's address (cudaGetSymbolAddress): issue it before any stream capture.  Asynchronous;
+ * makes no cudaMalloc/cudaFree.  DAB_NOALLOC_SPARE_ROUNDS retry rounds are always enqueued; a
+ * search that still overflowed writes id -1 / NaN (check the first id).
+ */
+#define DAB_NOALLOC_MAX_QUERIES 8
+#define DAB_NOALLOC_MAX_DIM 1024
+#define DAB_NOALLOC_SCRATCH_BYTES (560 * 1024)
+#define DAB_NOALLOC_SPARE_ROUNDS 2
+DAB_API int dab_search_noalloc(const void *rows_dev, int rows_dtype, const float *inv_norm_dev, int64_t n_rows, int dim,
+                               int64_t id_base, const float *q_dev, int Q, int k,
+                               const uint32_t *allow_bitmap_dev_or_null, float *out_scores_dev, int64_t *out_ids_dev,
+                               void *stream);
+
+/*
  * Measurement hooks (no counterpart in the reference, which only has the wall-clock
  * TimeDebugger of assistant/utils/debug.py:5-30 around the whole search).
  *   dab_launch_count      kernels this library has launched in this process
