@@ -81,7 +81,8 @@ struct SearchCtrl {
     int any_overflow;                // set by compact CTAs of this round
     int rounds_run;
     int overflow_events;             // statistics
-    int pad[2];
+    int inexact;                     // tensor path: more rows within the rescoring margin than can be kept
+    int pad;
 };
 
 // ---------------------------------------------------------------- PTX: mbarrier + bulk async copy (TMA)

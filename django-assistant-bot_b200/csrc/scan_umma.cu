@@ -1,12 +1,360 @@
-// scan_umma.cu - tcgen05 bf16 tensor-core scoring path (placeholder until the kernel lands).
+// scan_umma.cu - tensor-core scoring for larger query batches over bf16 stores (tcgen05 + TMEM + TMA).
+//
+// Scoring Q queries against N rows is a dense [N x D] x [D x Q] contraction; beyond a handful of
+// queries the CUDA cores cannot keep up with HBM, the 5th-gen tensor cores can.  Per CTA
+// (persistent, one per SM, cta_group::1):
+//   warp 0      TMA producer: the query block B [n_pad x D] bf16 is loaded ONCE into shared memory
+//               (it stays resident for the whole launch); corpus tiles A [128 rows x 64 cols] stream
+//               through a multi-stage ring (cp.async.bulk.tensor.2d, 128-byte swizzle, mbarriers)
+//   warp 1      MMA issuer: one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=n_pad, K=16)
+//               D/64 x 4 times per tile into one of two TMEM accumulator stages, then
+//               tcgen05.commit -> mbarrier frees the smem stage / publishes the accumulator
+//   warp 2      TMEM allocator (tcgen05.alloc / dealloc)
+//   warps 4-7   epilogue: tcgen05.ld the 128 x n_pad fp32 accumulator (lane = corpus row, column =
+//               query), scale by the row's 1/|row|, compare with the query's admission threshold,
+//               append the rare survivors to the candidate buffer.  Runs concurrently with the MMAs
+//               of the next tile (double-buffered TMEM).
+// The query is rounded to bf16 for this pass, so these scores are approximate: the selection keeps
+// everything within a rigorous margin of the k-th best and finish_rescore_kernel re-scores the kept
+// rows exactly in fp32 (select.cu).
+// HBM traffic = the corpus tile bytes, once; B is read from L2 once per CTA per launch.
+#include <cuda.h>
+
 #include "search.cuh"
 
 namespace dab {
-int umma_tile_rows() { return 128; }
-bool umma_supported(int, int) { return false; }
-void umma_release_maps(void *) {}
-int launch_scan_umma(const StoreView &, const uint32_t *, const SearchScratch &, int, bool, const LevelPlan &, int, void *, void *,
-                     cudaStream_t) {
-    return fail(DAB_E_INVALID, "tcgen05 path not built");
+
+namespace {
+
+constexpr int kTileRows = 128;      // UMMA M
+constexpr int kBlockK = 64;         // bf16 per 128-byte swizzle row
+constexpr int kUmmaK = 16;          // K of one tcgen05.mma for 16-bit inputs
+constexpr int kAStageBytes = kTileRows * kBlockK * 2;  // 16 KiB
+constexpr int kThreads = 256;
+constexpr int kMaxStages = 8;
+constexpr int kMinStages = 4;
+constexpr int kSmemBudget = 227 * 1024 - 2048;  // keep room for alignment slack
+
+// ---- PTX wrappers --------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
 }
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap *map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t *smem_out, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, 128-byte-swizzled shared-memory operand descriptor (sm_100 UMMA):
+//   [0,14) start address >> 4, [16,30) leading byte offset >> 4 (unused for swizzled K-major),
+//   [32,46) stride byte offset >> 4 (1024 B between 8-row groups), [46,48) version = 1,
+//   [61,64) layout = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(1024u >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// kind::f16 instruction descriptor: D=f32 (bits 4-5 = 1), A=B=bf16 (bits 7-9, 10-12 = 1), both K-major,
+// N>>3 at bits 17-22, M>>4 at bits 24-28
+__host__ __device__ constexpr uint32_t make_idesc(int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileRows >> 4) << 24);
+}
+
+// a spin that cannot hang the GPU: a lost arrival traps instead (the host sees a launch failure)
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity) {
+    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); spins++) {
+        if (spins > (1u << 28)) __trap();
+    }
+}
+
+__device__ __forceinline__ long long level_tile(const LevelPlan &plan, int lvl, long long j) {
+    const long long i = lvl == 0 ? j : j + j / (plan.growth - 1) + 1;
+    return i * plan.stride[lvl];
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
+                 const uint32_t *__restrict__ allow, SearchScratch sc, int q0, int nq, int n_pad, int stages,
+                 int tmem_cols, const __grid_constant__ LevelPlan plan) {
+    extern __shared__ unsigned char smem_raw[];
+    const int lvl = sc.ctrl->cur_level;
+    if (lvl >= plan.num_levels) return;
+    const long long ntiles = plan.tiles_in_level[lvl];
+    if ((long long)blockIdx.x >= ntiles) return;
+
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int num_kb = sv.dim / kBlockK;
+    const int b_kb_bytes = n_pad * kBlockK * 2;           // one k-block of the query operand
+    unsigned char *b_smem = smem;                          // [num_kb][n_pad rows x 128 B]
+    unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;  // [stages][128 rows x 128 B]
+    float *tau_s = reinterpret_cast<float *>(a_smem + (size_t)stages * kAStageBytes);  // [256]
+    uint64_t *full = reinterpret_cast<uint64_t *>(tau_s + DAB_MAX_QUERY_BATCH);
+    uint64_t *empty = full + kMaxStages;
+    uint64_t *b_full = empty + kMaxStages;
+    uint64_t *tmem_full = b_full + 1;                      // [2]
+    uint64_t *tmem_empty = tmem_full + 2;                  // [2]
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < stages; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(b_full, 1);
+        for (int a = 0; a < 2; a++) {
+            mbar_init(&tmem_full[a], 1);
+            mbar_init(&tmem_empty[a], 4);
+        }
+        fence_barrier_init();
+        prefetch_tmap(&tmap_rows);
+        prefetch_tmap(&tmap_q);
+    }
+    if (warp == 2) tmem_alloc(tmem_base_s, (uint32_t)tmem_cols);
+    for (int q = tid; q < DAB_MAX_QUERY_BATCH; q += kThreads) {
+        const bool live = q < nq && sc.active[q0 + q];
+        tau_s[q] = live ? key_score(sc.tau_key[q0 + q]) : INFINITY;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_s;
+    const long long my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            mbar_arrive_expect_tx(b_full, (uint32_t)(num_kb * b_kb_bytes));
+            for (int kb = 0; kb < num_kb; kb++) tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kBlockK, 0, b_full);
+            int s = 0;
+            uint32_t ph = 0;
+            for (long long it = 0; it < my_tiles; it++) {
+                const long long t = level_tile(plan, lvl, blockIdx.x + it * gridDim.x);
+                const int row0 = (int)(t * kTileRows);
+                for (int kb = 0; kb < num_kb; kb++) {
+                    mbar_wait_bounded(&empty[s], ph ^ 1u);
+                    mbar_arrive_expect_tx(&full[s], kAStageBytes);
+                    tma_load_2d(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s]);
+                    if (++s == stages) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(n_pad);
+            mbar_wait_bounded(b_full, 0);
+            tc_fence_after();
+            int s = 0;
+            uint32_t ph = 0;
+            for (long long it = 0; it < my_tiles; it++) {
+                const int a = (int)(it & 1);
+                const uint32_t aph = (uint32_t)((it >> 1) & 1);
+                mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);   // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)(a * n_pad);
+                for (int kb = 0; kb < num_kb; kb++) {
+                    mbar_wait_bounded(&full[s], ph);
+                    tc_fence_after();
+                    const uint64_t da = make_smem_desc(smem_u32(a_smem + (size_t)s * kAStageBytes));
+                    const uint64_t db = make_smem_desc(smem_u32(b_smem + (size_t)kb * b_kb_bytes));
+#pragma unroll
+                    for (int k = 0; k < kBlockK / kUmmaK; k++) {
+                        // advancing K by 16 elements = 32 bytes inside the swizzle atom: +2 in the address field
+                        umma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty[s]);                    // smem stage reusable once these MMAs finish
+                    if (++s == stages) { s = 0; ph ^= 1u; }
+                }
+                umma_commit(&tmem_full[a]);                    // accumulator complete
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------ epilogue
+        const int wq = warp & 3;                               // TMEM lane quarter this warp may read
+        for (long long it = 0; it < my_tiles; it++) {
+            const int a = (int)(it & 1);
+            const uint32_t aph = (uint32_t)((it >> 1) & 1);
+            const long long t = level_tile(plan, lvl, blockIdx.x + it * gridDim.x);
+            const long long row = t * kTileRows + wq * 32 + lane;
+            const float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
+            mbar_wait_bounded(&tmem_full[a], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pad);
+            for (int c0 = 0; c0 < n_pad; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(taddr + (uint32_t)c0, v);
+                tmem_ld_wait();
+                if (c0 < nq) {
+                    uint32_t pass = 0;
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        const float4 tq = *reinterpret_cast<const float4 *>(tau_s + c0 + j);
+                        pass |= (__uint_as_float(v[j + 0]) * rinv >= tq.x ? 1u : 0u) << (j + 0);
+                        pass |= (__uint_as_float(v[j + 1]) * rinv >= tq.y ? 1u : 0u) << (j + 1);
+                        pass |= (__uint_as_float(v[j + 2]) * rinv >= tq.z ? 1u : 0u) << (j + 2);
+                        pass |= (__uint_as_float(v[j + 3]) * rinv >= tq.w ? 1u : 0u) << (j + 3);
+                    }
+                    if (pass) {
+                        // slow path (rare once thresholds exist): exact key test, filter, append
+                        const bool ok = rinv > 0.f && (allow == nullptr || ((allow[row >> 5] >> (row & 31)) & 1u));
+                        if (ok) {
+#pragma unroll
+                            for (int j = 0; j < 16; j++) {
+                                if (pass & (1u << j)) {
+                                    const int q = q0 + c0 + j;
+                                    const uint64_t key = make_key(__uint_as_float(v[j]) * rinv, (uint32_t)row);
+                                    if (key > sc.tau_key[q]) {
+                                        const uint32_t pos = atomicAdd(&sc.cand_count[q], 1u);
+                                        if (pos < (uint32_t)kCandCap) sc.cand[(size_t)q * kCandCap + pos] = key;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[a]);
+        }
+    }
+    // ---------------------------------------------------------------- teardown
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, (uint32_t)tmem_cols);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D bf16 row-major [rows, dim] tensor, box = [box_rows x 64 columns], 128-byte swizzle, OOB rows read as zero
+int make_map(CUtensorMap *map, const void *base, uint64_t rows, uint64_t dim, uint32_t box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return fail(DAB_E_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    const cuuint64_t gdim[2] = {dim, rows};
+    const cuuint64_t gstride[1] = {dim * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)kBlockK, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(DAB_E_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return DAB_OK;
+}
+
+struct UmmaPlan {
+    int n_pad;
+    int stages;
+    int tmem_cols;
+    size_t smem;
+};
+
+bool plan_umma(int dim, int nq, UmmaPlan *out) {
+    const int n_pad = nq <= 16 ? 16 : (nq + 15) / 16 * 16;
+    const size_t b_bytes = (size_t)n_pad * dim * 2;
+    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 8) * sizeof(uint64_t) + 1024;
+    if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
+    int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
+    if (stages > kMaxStages) stages = kMaxStages;
+    int cols = 32;
+    while (cols < 2 * n_pad) cols <<= 1;
+    if (cols > 512) return false;
+    out->n_pad = n_pad;
+    out->stages = stages;
+    out->tmem_cols = cols;
+    out->smem = b_bytes + (size_t)stages * kAStageBytes + fixed;
+    return true;
+}
+
+}  // namespace
+
+int umma_tile_rows() { return kTileRows; }
+
+bool umma_supported(int dim, int dtype) {
+    UmmaPlan p;
+    return dtype == DAB_BF16 && dim % kBlockK == 0 && plan_umma(dim, 16, &p);
+}
+
+// the widest query block whose bf16 copy stays resident in shared memory next to >= 4 corpus stages
+int umma_queries_per_pass(int dim) {
+    int best = 0;
+    UmmaPlan p;
+    for (int n = 16; n <= DAB_MAX_QUERY_BATCH; n += 16)
+        if (plan_umma(dim, n, &p)) best = n;
+    return best;
+}
+
+void umma_release_maps(void *) {}
+
+int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq, const LevelPlan &plan,
+                     int num_sms, cudaStream_t st) {
+    UmmaPlan up;
+    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK || !plan_umma(sv.dim, nq, &up))
+        return fail(DAB_E_INVALID, "scan_umma: needs a bf16 store, dim % 64 == 0 and a query block that fits shared memory");
+    if (plan.tile_rows != kTileRows) return fail(DAB_E_INVALID, "scan_umma: level plan built for another tile size");
+    alignas(64) CUtensorMap tmap_rows, tmap_q;
+    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows)) return rc;
+    // B rows q0 .. q0+n_pad of the bf16 query copy; rows past the live queries hold stale data whose
+    // columns the epilogue ignores.  The buffer is 2*DAB_MAX_QUERY_BATCH rows long, so the box never leaves it.
+    if (int rc = make_map(&tmap_q, sc.qsplit + (size_t)q0 * sv.dim, (uint64_t)(2 * DAB_MAX_QUERY_BATCH - q0), (uint64_t)sv.dim,
+                          (uint32_t)up.n_pad))
+        return rc;
+    DAB_CUDA_OK(cudaFuncSetAttribute(scan_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)up.smem));
+    long long max_tiles = 0;
+    for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
+    const int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
+    scan_umma_kernel<<<grid, kThreads, up.smem, st>>>(tmap_rows, tmap_q, sv, allow, sc, q0, nq, up.n_pad, up.stages, up.tmem_cols,
+                                                      plan);
+    DAB_LAUNCH_OK();
+    return DAB_OK;
+}
+
 }  // namespace dab

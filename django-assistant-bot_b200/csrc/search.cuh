@@ -39,7 +39,9 @@ LevelPlan make_level_plan(int64_t n_rows, int tile_rows, int k_keep);
 
 // ---- kernels' host launchers (each returns DAB_OK or an error code) ----
 int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st);
-int launch_compact(const SearchScratch &sc, int nq, int k_keep, int num_levels, cudaStream_t st);
+int launch_compact(const SearchScratch &sc, int nq, int k, int num_levels, cudaStream_t st);
+// tensor path: keep every candidate within `margin` of the k-th best approximate score (<= k_cap)
+int launch_compact_margin(const SearchScratch &sc, int nq, int k, int k_cap, float margin, int num_levels, cudaStream_t st);
 int launch_finish_exact(const SearchScratch &sc, const StoreView &sv, int nq, int k, int num_levels, float *out_scores,
                         int64_t *out_ids, cudaStream_t st);
 int launch_finish_rescore(const SearchScratch &sc, const StoreView &sv, int nq, int k, int k_keep, int num_levels,
@@ -52,7 +54,8 @@ int launch_scan_simt(const StoreView &sv, const uint32_t *allow, const SearchScr
 
 int umma_tile_rows();
 bool umma_supported(int dim, int dtype);
-int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int nq, bool split,
-                     const LevelPlan &plan, int num_sms, void *tensor_map_rows, void *tensor_map_q, cudaStream_t st);
+int umma_queries_per_pass(int dim);
+int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
+                     const LevelPlan &plan, int num_sms, cudaStream_t st);
 
 }  // namespace dab

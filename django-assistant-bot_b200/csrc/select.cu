@@ -141,7 +141,7 @@ constexpr int kCompactThreads = 1024;
 // rows), keep the best k_keep, publish the new threshold; the last CTA to finish advances
 // (or repeats) the level - the host never has to look.
 __global__ void __launch_bounds__(kCompactThreads)
-compact_kernel(SearchScratch sc, int nq, int k_keep, int num_levels) {
+compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num_levels) {
     extern __shared__ uint64_t keys[];  // [kCandCap]
     __shared__ int s_scan[kCompactThreads / 32];
     __shared__ int s_is_last;
@@ -158,9 +158,9 @@ compact_kernel(SearchScratch sc, int nq, int k_keep, int num_levels) {
         uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
         for (int i = tid; i < P; i += kCompactThreads) keys[i] = i < n ? mine[i] : 0ull;
         bitonic_sort_desc<kCompactThreads>(keys, P);
-        // dedupe + keep the first k_keep unique keys (block-wide exclusive scan of the "is new" flags)
+        // dedupe + keep the first k_cap unique keys (block-wide exclusive scan of the "is new" flags)
         int kept_total = 0;
-        for (int base = 0; base < n && kept_total < k_keep; base += kCompactThreads) {
+        for (int base = 0; base < n && kept_total < k_cap; base += kCompactThreads) {
             const int i = base + tid;
             const uint64_t me = i < n ? keys[i] : 0ull;
             const int flag = (i < n && (i == 0 || keys[i - 1] != me)) ? 1 : 0;
@@ -173,21 +173,45 @@ compact_kernel(SearchScratch sc, int nq, int k_keep, int num_levels) {
             int block_total = 0;
             for (int w = 0; w < kCompactThreads / 32; w++) block_total += s_scan[w];
             const int pos = offset + __popc(ballot & ((1u << lane) - 1u));
-            if (flag && pos < k_keep) mine[pos] = me;
+            if (flag && pos < k_cap) mine[pos] = me;
             kept_total += block_total;
             __syncthreads();
         }
+        __syncthreads();  // mine[0..u) written by this block
+        const int u = min(kept_total, k_cap);
+        if (margin <= 0.f) {
+            // exact scores: keep the k best; the k-th key itself is the admission threshold
+            if (tid == 0) {
+                const int keep = min(u, k);
+                sc.cand_count[qi] = keep;
+                sc.tau_key[qi] = keep == k ? mine[k - 1] : kTauMin;  // valid only once k candidates exist
+            }
+        } else {
+            // approximate scores (tensor pass): everything within `margin` of the k-th best may still
+            // be in the exact top-k, so it is kept (up to k_cap) and admitted from now on
+            __shared__ int s_keep;
+            if (tid == 0) s_keep = u;
+            __syncthreads();
+            if (u >= k) {
+                const uint64_t thr_key = make_key(key_score(mine[k - 1]) - margin, 0xffffffffu);
+                for (int i = tid; i < u; i += kCompactThreads) {
+                    if (mine[i] > thr_key && (i + 1 == u || mine[i + 1] <= thr_key)) s_keep = i + 1;
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    sc.tau_key[qi] = thr_key;
+                    // more rows inside the margin than we can keep: the exactness guarantee is gone
+                    if (s_keep == u && (kept_total > k_cap || ovf) && u == k_cap) atomicExch(&ctrl->inexact, 1);
+                }
+            } else if (tid == 0) {
+                sc.tau_key[qi] = kTauMin;
+            }
+            __syncthreads();
+            if (tid == 0) sc.cand_count[qi] = s_keep;
+        }
         if (tid == 0) {
-            const int keep = min(kept_total, k_keep);
-            sc.cand_count[qi] = keep;
             sc.overflowed[qi] = ovf ? 1 : 0;
             if (ovf) atomicExch(&ctrl->any_overflow, 1);
-        }
-        __syncthreads();  // mine[0..keep) written by this block
-        if (tid == 0) {
-            const int keep = min(kept_total, k_keep);
-            // a threshold is only valid once k_keep real candidates exist
-            sc.tau_key[qi] = keep == k_keep ? mine[k_keep - 1] : kTauMin;
         }
     }
     // ---- round control by the last CTA
@@ -388,14 +412,14 @@ int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int
     return DAB_OK;
 }
 
-int launch_compact(const SearchScratch &sc, int nq, int k_keep, int num_levels, cudaStream_t st) {
-    static bool attr_set = false;
+int launch_compact(const SearchScratch &sc, int nq, int k, int num_levels, cudaStream_t st) {
+    return launch_compact_margin(sc, nq, k, k, 0.f, num_levels, st);
+}
+
+int launch_compact_margin(const SearchScratch &sc, int nq, int k, int k_cap, float margin, int num_levels, cudaStream_t st) {
     const int smem = kCandCap * sizeof(uint64_t);
-    if (!attr_set) {
-        DAB_CUDA_OK(cudaFuncSetAttribute(compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
-    }
-    compact_kernel<<<nq, kCompactThreads, smem, st>>>(sc, nq, k_keep, num_levels);
+    DAB_CUDA_OK(cudaFuncSetAttribute(compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    compact_kernel<<<nq, kCompactThreads, smem, st>>>(sc, nq, k, k_cap, margin, num_levels);
     DAB_LAUNCH_OK();
     return DAB_OK;
 }
@@ -435,12 +459,8 @@ extern "C" DAB_API int dab_merge_topk(const float *gathered_scores, const int64_
     int P = 32;
     while (P < R * k) P <<= 1;
     const int smem = P * (int)(sizeof(uint32_t) + sizeof(int64_t));
-    static bool attr_set = false;
-    if (!attr_set) {
-        DAB_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kMergeMax * (int)(sizeof(uint32_t) + sizeof(int64_t))));
-        attr_set = true;
-    }
+    DAB_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kMergeMax * (int)(sizeof(uint32_t) + sizeof(int64_t))));
     merge_topk_kernel<<<Q, kMergeThreads, smem, static_cast<cudaStream_t>(stream)>>>(gathered_scores, gathered_ids, R, Q, k,
                                                                                       out_scores, out_ids);
     DAB_LAUNCH_OK();

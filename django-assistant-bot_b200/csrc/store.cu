@@ -285,22 +285,28 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
     int path = s->path;
     if (path == 0) path = (umma_supported(sv.dim, sv.dtype) && nq > simt_queries_per_pass(sv.dim, sv.dtype)) ? 2 : 1;
     if (path == 2) {
-        // tensor path: hi+lo split of the query keeps the pass within ~1e-7 of fp32 while it is
-        // HBM-bound (2*nq <= 256 MMA columns); beyond that one bf16 pass plus a wider margin.
-        const bool split = 2 * nq <= DAB_MAX_QUERY_BATCH;
-        int k_keep = split ? k + 16 : 2 * k + 64;
-        if (k_keep > kCandCap / 4) k_keep = kCandCap / 4;
-        if (k_keep < k) k_keep = k;
-        const LevelPlan plan = make_level_plan(sv.n, umma_tile_rows(), k_keep);
+        // Tensor path.  The pass scores with the query rounded to bf16: per element |dq| <= 2^-8 |q|, so by
+        // Cauchy-Schwarz |approx - exact| <= 2^-8 for unit vectors, plus fp32 accumulation noise
+        // (<= dim * 2^-24).  Everything within twice that bound of the k-th best approximate score
+        // can still belong to the exact top-k: it is kept (up to kKeepCap) and rescored in fp32.
+        const float eps = 0.00390625f + (float)sv.dim * 6e-8f;
+        const float margin = 2.0f * eps;
+        const int k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
+        // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
+        const LevelPlan plan = make_level_plan(sv.n, umma_tile_rows(), 4 * k < k_cap ? 4 * k : k_cap);
+        const int qpass = umma_queries_per_pass(sv.dim);
         *num_levels_out = plan.num_levels;
         if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st)) return rc;
         for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
-            ScanTimer tm(s->prof, st);
-            if (int rc = launch_scan_umma(sv, allow, sc, nq, split, plan, s->num_sms, s->umma_maps, nullptr, st)) return rc;
-            tm.stop();
-            if (int rc = launch_compact(sc, nq, k_keep, plan.num_levels, st)) return rc;
+            for (int q0 = 0; q0 < nq; q0 += qpass) {
+                const int n_sub = nq - q0 < qpass ? nq - q0 : qpass;
+                ScanTimer tm(s->prof, st);
+                if (int rc = launch_scan_umma(sv, allow, sc, q0, n_sub, plan, s->num_sms, st)) return rc;
+                tm.stop();
+            }
+            if (int rc = launch_compact_margin(sc, nq, k, k_cap, margin, plan.num_levels, st)) return rc;
         }
-        return launch_finish_rescore(sc, sv, nq, k, k_keep, plan.num_levels, out_scores, out_ids, st);
+        return launch_finish_rescore(sc, sv, nq, k, k_cap, plan.num_levels, out_scores, out_ids, st);
     }
     const int qb = simt_queries_per_pass(sv.dim, sv.dtype);
     const LevelPlan plan = make_level_plan(sv.n, simt_tile_rows(sv.dim, sv.dtype), k);

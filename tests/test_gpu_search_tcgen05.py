@@ -1,0 +1,60 @@
+"""Parity of the tcgen05 (bf16 tensor-core) scoring path + exact fp32 rescoring with the oracle.
+The tensor pass ranks with bf16-rounded queries; the final ids/scores must still meet the exact bar."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import search_ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _run(N, D, Q, k, seed, path="tcgen05", planted=False):
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(seed)
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    if planted:
+        # near-duplicates of the queries: a dense cluster of scores inside the rescoring margin
+        for qi in range(min(Q, 4)):
+            idx = torch.randint(0, N, (300,), generator=g)
+            rows[idx] = queries[qi] + 0.02 * torch.randn(300, D, generator=g)
+        rows[7] = 0
+    store = ops.ChunkStore(N, D, torch.bfloat16, DEV)
+    store.set_path(path)
+    store.append(rows.to(DEV))
+    stored = rows.to(torch.bfloat16).float().numpy()
+    scores, ids = store.search(queries.to(DEV), k)
+    S = search_ref.exact_scores(stored, queries.numpy())
+    ids, scores = ids.cpu().numpy(), scores.cpu().numpy()
+    for qi in range(Q):
+        search_ref.check_topk_parity(S[qi], ids[qi], scores[qi], k)
+    store.close()
+    return ids, scores
+
+
+@pytest.mark.parametrize("N,D,Q,k", [(20_000, 64, 5, 10), (50_000, 768, 16, 10), (100_000, 768, 64, 100),
+                                     (60_001, 1024, 64, 100), (30_000, 384, 33, 5), (200_000, 768, 80, 10),
+                                     (300, 128, 8, 10), (40_000, 768, 200, 20)])
+def test_tcgen05_parity(N, D, Q, k):
+    _run(N, D, Q, k, seed=N + D + Q + k)
+
+
+def test_tcgen05_dense_score_cluster_and_zero_row():
+    _run(80_000, 768, 8, 50, seed=77, planted=True)
+
+
+def test_auto_path_picks_tensor_cores_for_batches():
+    ids_auto, sc_auto = _run(50_000, 768, 32, 10, seed=5, path="auto")
+    ids_simt, sc_simt = _run(50_000, 768, 32, 10, seed=5, path="simt")
+    np.testing.assert_array_equal(ids_auto, ids_simt)
+    np.testing.assert_allclose(sc_auto, sc_simt, rtol=1e-5, atol=1e-6)
+
+
+def test_tcgen05_rejected_for_fp32_store():
+    from dab_b200 import DabError, ops
+    store = ops.ChunkStore(100, 768, torch.float32, DEV)
+    with pytest.raises(DabError, match="bf16 store"):
+        store.set_path("tcgen05")
+    store.close()
