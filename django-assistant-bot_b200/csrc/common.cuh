@@ -82,7 +82,9 @@ struct SearchCtrl {
     int rounds_run;
     int overflow_events;             // statistics
     int inexact;                     // tensor path: more rows within the rescoring margin than can be kept
-    int pad;
+    int sticky_incomplete;           // some chunk of this search call ended before its last level
+    int sticky_inexact;              // some chunk of this search call raised `inexact`
+    int pad[3];
 };
 
 // ---------------------------------------------------------------- PTX: mbarrier + bulk async copy (TMA)

@@ -38,7 +38,8 @@ struct StoreView {
 LevelPlan make_level_plan(int64_t n_rows, int tile_rows, int k_keep);
 
 // ---- kernels' host launchers (each returns DAB_OK or an error code) ----
-int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st);
+int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st,
+                        bool first_chunk = true);
 int launch_compact(const SearchScratch &sc, int nq, int k, int num_levels, cudaStream_t st);
 // tensor path: keep every candidate within `margin` of the k-th best approximate score (<= k_cap)
 int launch_compact_margin(const SearchScratch &sc, int nq, int k, int k_cap, float margin, int num_levels, cudaStream_t st);

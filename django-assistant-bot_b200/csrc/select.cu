@@ -76,7 +76,7 @@ namespace {
 
 // ---------------------------------------------------------------- begin: normalise queries, reset state
 __global__ void __launch_bounds__(128)
-search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int want_split) {
+search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int want_split, int first_chunk) {
     const int qi = blockIdx.x;
     const int tid = threadIdx.x;
     __shared__ float red[4];
@@ -109,6 +109,11 @@ search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int 
         sc.overflowed[qi] = 0;
         if (qi == 0) {
             SearchCtrl c = {};
+            if (!first_chunk) {  // a later chunk of the same search call keeps the sticky verdicts
+                c.sticky_incomplete = sc.ctrl->sticky_incomplete;
+                c.sticky_inexact = sc.ctrl->sticky_inexact;
+                c.overflow_events = sc.ctrl->overflow_events;
+            }
             *sc.ctrl = c;
         }
     }
@@ -249,6 +254,7 @@ finish_exact_kernel(SearchScratch sc, StoreView sv, int k, int num_levels, float
     const bool done = sc.ctrl->cur_level >= num_levels;
     const int cnt = done ? min((int)sc.cand_count[qi], k) : 0;
     const uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
+    if (qi == 0 && threadIdx.x == 0 && !done) sc.ctrl->sticky_incomplete = 1;
     for (int j = threadIdx.x; j < k; j += blockDim.x) {
         float s;
         int64_t id;
@@ -279,6 +285,10 @@ finish_rescore_kernel(SearchScratch sc, StoreView sv, int k, int k_keep, int num
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool done = sc.ctrl->cur_level >= num_levels;
     const int cnt = done ? min((int)sc.cand_count[qi], k_keep) : 0;
+    if (qi == 0 && tid == 0) {
+        if (!done) sc.ctrl->sticky_incomplete = 1;
+        if (sc.ctrl->inexact) sc.ctrl->sticky_inexact = 1;
+    }
     int P = 32;
     while (P < cnt) P <<= 1;
     const uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
@@ -406,8 +416,9 @@ merge_topk_kernel(const float *__restrict__ gs, const int64_t *__restrict__ gi, 
 
 }  // namespace
 
-int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st) {
-    search_begin_kernel<<<nq, 128, 0, st>>>(sc, q_dev, dim, want_split ? 1 : 0);
+int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st,
+                        bool first_chunk) {
+    search_begin_kernel<<<nq, 128, 0, st>>>(sc, q_dev, dim, want_split ? 1 : 0, first_chunk ? 1 : 0);
     DAB_LAUNCH_OK();
     return DAB_OK;
 }

@@ -56,6 +56,7 @@ struct dab_store {
     int last_num_levels = 0;
     void *umma_maps = nullptr;  // tensor maps of the tcgen05 path (built lazily)
     dab_profile prof;
+    dab::SearchCtrl *status_host = nullptr;  // pinned landing buffer of dab_store_search_status
     std::mutex mu;
 };
 
@@ -173,6 +174,8 @@ extern "C" DAB_API int dab_store_create(dab_store **out, int device, int64_t cap
     int sms = 0;
     if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bail("attr", e);
     s->num_sms = sms;
+    if ((e = cudaHostAlloc(reinterpret_cast<void **>(&s->status_host), sizeof(SearchCtrl), cudaHostAllocDefault)) != cudaSuccess)
+        return bail("status buffer", e);
     *out = s;
     return DAB_OK;
 }
@@ -185,6 +188,7 @@ extern "C" DAB_API void dab_store_destroy(dab_store *s) {
     cudaFree(s->inv_norm);
     cudaFree(s->ids);
     cudaFree(s->scratch_base);
+    if (s->status_host) cudaFreeHost(s->status_host);
     delete s;
 }
 
@@ -281,7 +285,8 @@ struct ScanTimer {
 
 // The rounds of one query chunk (<= 256 queries), all enqueued on `st` without a host sync.
 int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc, const float *q_dev, int nq, int k,
-                     const uint32_t *allow, float *out_scores, int64_t *out_ids, int *num_levels_out, cudaStream_t st) {
+                     const uint32_t *allow, float *out_scores, int64_t *out_ids, int *num_levels_out, cudaStream_t st,
+                     bool first_chunk) {
     int path = s->path;
     if (path == 0) path = (umma_supported(sv.dim, sv.dtype) && nq > simt_queries_per_pass(sv.dim, sv.dtype)) ? 2 : 1;
     if (path == 2) {
@@ -296,7 +301,7 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
         const LevelPlan plan = make_level_plan(sv.n, umma_tile_rows(), 4 * k < k_cap ? 4 * k : k_cap);
         const int qpass = umma_queries_per_pass(sv.dim);
         *num_levels_out = plan.num_levels;
-        if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st)) return rc;
+        if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st, first_chunk)) return rc;
         for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
             for (int q0 = 0; q0 < nq; q0 += qpass) {
                 const int n_sub = nq - q0 < qpass ? nq - q0 : qpass;
@@ -311,7 +316,7 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
     const int qb = simt_queries_per_pass(sv.dim, sv.dtype);
     const LevelPlan plan = make_level_plan(sv.n, simt_tile_rows(sv.dim, sv.dtype), k);
     *num_levels_out = plan.num_levels;
-    if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, false, st)) return rc;
+    if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, false, st, first_chunk)) return rc;
     for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
         for (int q0 = 0; q0 < nq; q0 += qb) {
             const int n_sub = nq - q0 < qb ? nq - q0 : qb;
@@ -365,7 +370,7 @@ extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q,
         const int nq = Q - q0 < DAB_MAX_QUERY_BATCH ? Q - q0 : DAB_MAX_QUERY_BATCH;
         int levels = 0;
         if (int rc = run_search_chunk(s, sv, s->scratch, q_dev + (size_t)q0 * s->dim, nq, k, allow,
-                                      out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, &levels, st))
+                                      out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, &levels, st, q0 == 0))
             return rc;
         s->last_num_levels = levels;
     }
@@ -377,12 +382,19 @@ extern "C" DAB_API int dab_store_search_status(dab_store *s, void *stream) {
     std::lock_guard<std::mutex> g(s->mu);
     DAB_CUDA_OK(cudaSetDevice(s->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    SearchCtrl c;
+    if (s->last_num_levels == 0) {  // nothing searched yet, or the store was empty
+        DAB_CUDA_OK(cudaStreamSynchronize(st));
+        return DAB_OK;
+    }
+    SearchCtrl &c = *s->status_host;  // pinned: the copy is a plain DMA, no staging
     DAB_CUDA_OK(cudaMemcpyAsync(&c, s->scratch.ctrl, sizeof(c), cudaMemcpyDeviceToHost, st));
     DAB_CUDA_OK(cudaStreamSynchronize(st));
-    if (s->last_num_levels > 0 && c.cur_level < s->last_num_levels)
+    if (c.sticky_incomplete)
         return fail(DAB_E_INCOMPLETE, "search incomplete: candidate buffer overflowed " + std::to_string(c.overflow_events) +
                                           " time(s); raise dab_store_set_spare_rounds and search again");
+    if (c.sticky_inexact)
+        return fail(DAB_E_INEXACT, "more than " + std::to_string(kCandCap / 4) +
+                                       " rows lie within the bf16 rescoring margin of the k-th best; search again on the CUDA-core path");
     return DAB_OK;
 }
 

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libdab_b200.so")
 
 DAB_F32, DAB_BF16 = 0, 1
 DAB_MASK_U8, DAB_MASK_I32, DAB_MASK_I64 = 0, 1, 2
-DAB_OK, DAB_E_INVALID, DAB_E_CUDA, DAB_E_DIM, DAB_E_CAPACITY, DAB_E_INCOMPLETE = range(6)
+DAB_OK, DAB_E_INVALID, DAB_E_CUDA, DAB_E_DIM, DAB_E_CAPACITY, DAB_E_INCOMPLETE, DAB_E_INEXACT = range(7)
 DAB_MAX_K = 2048
 DAB_MAX_QUERY_BATCH = 256
 

@@ -97,6 +97,7 @@ class ChunkStore:
         self.dim = int(dim)
         self.dtype = dtype
         self._h = _lib.c_void_p()
+        self._path = 0
         self._lock = threading.Lock()
         check(lib().dab_store_create(_lib.ctypes.byref(self._h), self.device.index, int(capacity), int(dim), _DTYPES[dtype]))
         if id_base:
@@ -125,7 +126,9 @@ class ChunkStore:
         check(lib().dab_store_reset(self._h))
 
     def set_path(self, path: str) -> None:
-        check(lib().dab_store_set_path(self._h, {"auto": 0, "simt": 1, "tcgen05": 2}[path]))
+        code = {"auto": 0, "simt": 1, "tcgen05": 2}[path]
+        check(lib().dab_store_set_path(self._h, code))
+        self._path = code
 
     def set_spare_rounds(self, n: int) -> None:
         check(lib().dab_store_set_spare_rounds(self._h, int(n)))
@@ -193,21 +196,30 @@ class ChunkStore:
         candidate buffer (adversarial row order) repeats with spare rounds until complete."""
         with self._lock:
             spare = 0
-            while True:
-                scores, ids = self.search_async(queries, k, allow_bitmap)
-                with torch.cuda.device(self.device):
-                    rc = lib().dab_store_search_status(self._h, _stream(self.device))
-                incomplete = rc == _lib.DAB_E_INCOMPLETE or bool(torch.isnan(scores).any())
-                if not incomplete:
-                    check(rc)
-                    if spare:
-                        self.set_spare_rounds(0)
-                    return scores, ids
-                spare = 4 if spare == 0 else spare * 2
-                if spare > 64:
-                    check(rc)
-                    raise DabError(_lib.DAB_E_INCOMPLETE, "search did not complete within 64 spare rounds")
-                self.set_spare_rounds(spare)
+            forced_simt = False
+            try:
+                while True:
+                    scores, ids = self.search_async(queries, k, allow_bitmap)
+                    with torch.cuda.device(self.device):
+                        rc = lib().dab_store_search_status(self._h, _stream(self.device))
+                    if rc == _lib.DAB_E_INEXACT and not forced_simt:
+                        # more rows inside the bf16 rescoring margin than the tensor pass can keep:
+                        # answer this call on the exact CUDA-core path instead
+                        lib().dab_store_set_path(self._h, 1)
+                        forced_simt = True
+                        continue
+                    if rc != _lib.DAB_E_INCOMPLETE:
+                        check(rc)
+                        return scores, ids
+                    spare = 4 if spare == 0 else spare * 2
+                    if spare > 64:
+                        raise DabError(_lib.DAB_E_INCOMPLETE, "search did not complete within 64 spare rounds")
+                    self.set_spare_rounds(spare)
+            finally:
+                if spare:
+                    self.set_spare_rounds(0)
+                if forced_simt:
+                    lib().dab_store_set_path(self._h, self._path)
 
 
 def merge_topk(gathered_scores: torch.Tensor, gathered_ids: torch.Tensor):

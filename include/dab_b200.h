@@ -51,6 +51,7 @@ typedef struct dab_store dab_store;
 #define DAB_E_DIM 3         /* "different vector dimensions", like pgvector raises */
 #define DAB_E_CAPACITY 4    /* store full / size beyond a stated maximum */
 #define DAB_E_INCOMPLETE 5  /* a search did not finish its scan rounds (see dab_store_search_status) */
+#define DAB_E_INEXACT 6     /* tensor path: too many rows inside the rescoring margin; use the CUDA-core path */
 
 /* limits */
 #define DAB_MAX_K 2048           /* largest n of a search; the reference uses 1, 5, 10, 250 */
@@ -130,7 +131,8 @@ DAB_API int dab_store_set_id_base(dab_store *s, int64_t id_base);
  */
 DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
                      float *out_scores_dev, int64_t *out_ids_dev, void *stream);
-/* Synchronises `stream`, returns DAB_OK or DAB_E_INCOMPLETE for the last search on `s`. */
+/* Synchronises `stream`; DAB_OK, DAB_E_INCOMPLETE or DAB_E_INEXACT for the last search call on `s`
+ * (all of its query chunks). */
 DAB_API int dab_store_search_status(dab_store *s, void *stream);
 /* extra scan rounds enqueued per search for overflow retries (default 0) */
 DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds);

@@ -159,6 +159,25 @@ def check_topk_parity(S_row: np.ndarray, got_ids: np.ndarray, got_scores: np.nda
             f"rank {pos}: score {got_scores[pos]!r} vs oracle {S_row[g]!r}")
 
 
+def merge_topk_lists(gathered_scores: np.ndarray, gathered_ids: np.ndarray, k: int):
+    """Checker for the cross-shard merge: ``[R,Q,k]`` per-shard lists -> ``[Q,k]`` under
+    (score desc, id asc); id -1 marks an empty slot.  The single-table ORDER BY ... LIMIT n of
+    search_service.py:192-194 applied to the union of the shard results."""
+    gs = np.asarray(gathered_scores, dtype=np.float64)
+    gi = np.asarray(gathered_ids, dtype=np.int64)
+    R, Q, _ = gs.shape
+    out_s = np.full((Q, k), -np.inf)
+    out_i = np.full((Q, k), -1, dtype=np.int64)
+    for q in range(Q):
+        s, i = gs[:, q].ravel(), gi[:, q].ravel()
+        keep = i >= 0
+        s, i = s[keep], i[keep]
+        order = np.lexsort((i, -s))[:k]
+        out_s[q, :len(order)] = s[order]
+        out_i[q, :len(order)] = i[order]
+    return out_s, out_i
+
+
 # ----------------------------------------------------------------------------- doc-level aggregation
 
 

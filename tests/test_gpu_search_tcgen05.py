@@ -45,6 +45,32 @@ def test_tcgen05_dense_score_cluster_and_zero_row():
     _run(80_000, 768, 8, 50, seed=77, planted=True)
 
 
+def test_tcgen05_inexact_falls_back_to_exact_path():
+    """5000 near-copies of a query all sit inside the bf16 rescoring margin of the k-th best: more
+    than the 2048 candidates the tensor pass may keep.  The raw call must say DAB_E_INEXACT; the
+    checked search must answer on the CUDA-core path and still be exact."""
+    from dab_b200 import _lib, ops
+    g = torch.Generator().manual_seed(21)
+    N, D, Q, k = 60_000, 768, 8, 10
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    idx = torch.randperm(N, generator=g)[:5000]
+    rows[idx] = queries[0] + 0.001 * torch.randn(5000, D, generator=g)
+    store = ops.ChunkStore(N, D, torch.bfloat16, DEV)
+    store.set_path("tcgen05")
+    store.set_spare_rounds(8)
+    store.append(rows.to(DEV))
+    store.search_async(queries.to(DEV), k)
+    rc = _lib.lib().dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
+    assert rc == _lib.DAB_E_INEXACT, _lib.lib().dab_last_error()
+    store.set_spare_rounds(0)
+    scores, ids = store.search(queries.to(DEV), k)
+    S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), queries.numpy())
+    for qi in range(Q):
+        search_ref.check_topk_parity(S[qi], ids[qi].cpu().numpy(), scores[qi].cpu().numpy(), k)
+    store.close()
+
+
 def test_auto_path_picks_tensor_cores_for_batches():
     ids_auto, sc_auto = _run(50_000, 768, 32, 10, seed=5, path="auto")
     ids_simt, sc_simt = _run(50_000, 768, 32, 10, seed=5, path="simt")

@@ -1,0 +1,48 @@
+"""Two-GPU check of the sharded store (NCCL all-gather + dab_merge_topk).  Skipped on a 1-GPU box."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, os.path.join(ROOT, "django-assistant-bot_b200")); sys.path.insert(0, ROOT)
+import numpy as np, torch, torch.distributed as dist
+from dab_b200 import sharded
+from oracle import search_ref
+rank = int(os.environ["RANK"]); torch.cuda.set_device(rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+N, D, Q, k = 200_000, 768, 16, 50
+g = torch.Generator().manual_seed(1)
+rows = torch.randn(N, D, generator=g); queries = torch.randn(Q, D, generator=g)
+st = sharded.ShardedStore(N, D, torch.bfloat16, torch.device("cuda", rank))
+st.append_local(rows[st.lo:st.hi].cuda())
+s, i = st.search(queries.cuda(), k)
+S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), queries.numpy())
+for q in range(Q):
+    search_ref.check_topk_parity(S[q], i[q].cpu().numpy(), s[q].cpu().numpy(), k)
+dist.barrier(); dist.destroy_process_group(); print("rank", rank, "ok")
+'''
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_gpu_sharded_search():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), "-c", "ROOT=%r\n%s" % (ROOT, WORKER)]
+    # torch.distributed.run has no -c: write the worker to a temp file instead
+    import tempfile
+    with tempfile.NamedTemporaryFile("w", suffix=".py", delete=False) as f:
+        f.write("ROOT=%r\n%s" % (ROOT, WORKER))
+        path = f.name
+    cmd = cmd[:-2] + [path]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
