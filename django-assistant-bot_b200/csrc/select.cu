@@ -165,7 +165,8 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
         bitonic_sort_desc<kCompactThreads>(keys, P);
         // dedupe + keep the first k_cap unique keys (block-wide exclusive scan of the "is new" flags)
         int kept_total = 0;
-        for (int base = 0; base < n && kept_total < k_cap; base += kCompactThreads) {
+        int base = 0;
+        for (; base < n && kept_total < k_cap; base += kCompactThreads) {
             const int i = base + tid;
             const uint64_t me = i < n ? keys[i] : 0ull;
             const int flag = (i < n && (i == 0 || keys[i - 1] != me)) ? 1 : 0;
@@ -206,7 +207,8 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
                 if (tid == 0) {
                     sc.tau_key[qi] = thr_key;
                     // more rows inside the margin than we can keep: the exactness guarantee is gone
-                    if (s_keep == u && (kept_total > k_cap || ovf) && u == k_cap) atomicExch(&ctrl->inexact, 1);
+                    // (sorted keys were left unread, or more unique keys than slots, or the buffer itself overflowed)
+                    if (s_keep == u && u == k_cap && (base < n || kept_total > k_cap || ovf)) atomicExch(&ctrl->inexact, 1);
                 }
             } else if (tid == 0) {
                 sc.tau_key[qi] = kTauMin;
