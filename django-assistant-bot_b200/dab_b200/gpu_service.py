@@ -1,0 +1,73 @@
+"""The embeddings endpoint of the GPU service, same HTTP contract as the reference.
+
+Mirrors ``gpu_service/main.py`` of the reference for the hot path only:
+``EmbeddingRequest`` (:34-36), the model registry + lifespan loader (:52-72) and
+``POST /embeddings/`` (:75-86): lower-cased model lookup, 400 "Model is not supported" for an
+unknown model, ``{"embeddings": [[float]]}`` on success, 500 with ``str(e)`` on any failure.
+``/dialog/`` (LLM generation) is out of scope.  The embedder behind it pools on the B200
+(``dab_b200.embedders.B200TransformersEmbedder``).
+
+Run like the reference (gunicorn_conf.py:9-16):
+    gunicorn -k uvicorn.workers.UvicornWorker "dab_b200.gpu_service:create_app()"
+"""
+from __future__ import annotations
+
+import logging
+from contextlib import asynccontextmanager
+from typing import Dict, Iterable, List, Optional
+
+from fastapi import FastAPI, HTTPException
+from pydantic import BaseModel
+
+logger = logging.getLogger(__name__)
+
+# gpu_service/models.py:1-3 of the reference
+DEFAULT_EMBEDDER_MODELS = ["sberbank-ai/ruBert-base"]
+
+
+class EmbeddingRequest(BaseModel):
+    model: str
+    texts: List[str]
+
+
+def create_app(embedder_models: Optional[Iterable[str]] = None, embedders: Optional[Dict[str, object]] = None,
+               embedder_factory=None) -> FastAPI:
+    """``embedders``: pre-built ``{name: AIEmbedder}`` (tests, custom loading); otherwise every name
+    in ``embedder_models`` is loaded at start-up with ``embedder_factory`` (default
+    ``B200TransformersEmbedder``); load failures are logged and skipped, after which that model
+    answers 400 - exactly the reference's behaviour (main.py:60-63,77-79)."""
+    registry: Dict[str, object] = {}
+    if embedders:
+        registry.update({k.lower(): v for k, v in embedders.items()})
+    names = list(DEFAULT_EMBEDDER_MODELS if embedder_models is None and not embedders else (embedder_models or []))
+
+    @asynccontextmanager
+    async def lifespan(app: FastAPI):
+        logger.info("App is starting.")
+        factory = embedder_factory
+        if factory is None and names:
+            from .embedders import B200TransformersEmbedder as factory  # noqa: N813
+        for model in names:
+            try:
+                registry[model.lower()] = factory(model)
+            except Exception as e:  # same policy as the reference: log, skip, answer 400 later
+                logger.exception(f"Failed to load embedder {model}: {e}")
+        logger.info("App initialized.")
+        yield
+
+    app = FastAPI(lifespan=lifespan)
+    app.state.embedders = registry
+
+    @app.post("/embeddings/")
+    async def get_embeddings(request: EmbeddingRequest):
+        model = request.model.lower()
+        if model not in registry:
+            raise HTTPException(status_code=400, detail="Model is not supported")
+        try:
+            embeddings = await registry[model].embeddings(request.texts)
+            return {"embeddings": embeddings}
+        except Exception as e:
+            logger.exception(f"Failed to get response: {e}")
+            raise HTTPException(status_code=500, detail=str(e))
+
+    return app

@@ -1,0 +1,319 @@
+"""RAG similarity search with the reference's API, executed on the B200 store.
+
+Mirror of ``assistant/rag/services/search_service.py``: the same function names, arguments and
+return shapes - ``_objects_embedding_search`` (:185-196), ``embedding_search_documents /
+_questions / _sentences`` (:161-182), ``embedding_search`` (:111-152), ``get_embedding``
+(:155-158), ``cosine_similarity`` / ``embeddings_similarity`` (:17-21, :32-35).  The one thing
+that changes is where ``ORDER BY embedding <=> q LIMIT n`` runs: not in PostgreSQL+pgvector but in
+``dab_store_search`` over a device-resident copy of the embedding column (``DeviceTable``).
+
+Two kinds of ``qs`` are accepted:
+
+* ``ChunkQuerySet`` - the stand-in used where Django is not installed (this repository's tests and
+  benchmarks): a filterable view over a ``DeviceTable``;
+* a Django ``QuerySet`` (duck-typed: ``.model``, ``.values_list('pk', flat=True)``,
+  ``.model.objects.in_bulk``) - the table registered for ``(model label, field)`` is searched with
+  the queryset's pks as the allow-set, and real model instances come back with ``.distance`` set.
+
+There is no CPU path: a search without a CUDA device raises ``DabError``.
+"""
+from __future__ import annotations
+
+import asyncio
+import logging
+from collections import defaultdict
+from typing import Any, Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import ops
+from ._lib import DabError
+
+logger = logging.getLogger(__name__)
+
+EMBEDDING_DIM = 768  # assistant/storage/models.py:13,23 ("for RuBert")
+
+
+# --------------------------------------------------------------------------- small NumPy helpers
+def cosine_similarity(a, b):
+    """search_service.py:17-21 - two-vector utility used by the emb_test command, not the scan."""
+    a = np.asarray(a)
+    b = np.asarray(b)
+    return np.dot(a, b) / (np.linalg.norm(a) * np.linalg.norm(b))
+
+
+def embeddings_similarity(a: List[float], b: List[float]) -> float:
+    """search_service.py:32-35."""
+    return cosine_similarity(np.array(a), np.array(b))
+
+
+# --------------------------------------------------------------------------- the device table
+class ChunkRow:
+    """One search hit when no ORM is present; attribute-compatible with a
+    ``BaseEmbeddingModel`` row (assistant/storage/models.py:19-29) plus ``.distance``."""
+    __slots__ = ("id", "pk", "document_id", "text", "order", "distance")
+
+    def __init__(self, pk, document_id, text, order, distance):
+        self.id = self.pk = pk
+        self.document_id = document_id
+        self.text = text
+        self.order = order
+        self.distance = distance
+
+    def __repr__(self):
+        return f"ChunkRow(id={self.id}, document_id={self.document_id}, distance={self.distance:.6f})"
+
+
+class DeviceTable:
+    """Device-resident copy of one embedding column: ``Sentence.embedding``,
+    ``Question.embedding`` (assistant/storage/models.py:32-58) or ``Document.content_embedding``
+    (:13).  Rows with a NULL embedding are simply not added (the column is nullable, :23).
+
+    Host side keeps what the ORM would: pk, document_id, text, order, and any columns the
+    reference filters on (e.g. ``document__wiki__bot``), as NumPy arrays aligned with store rows.
+    """
+
+    def __init__(self, capacity: int, dim: int = EMBEDDING_DIM, dtype: torch.dtype = torch.float32, device=None):
+        self.store = ops.ChunkStore(capacity, dim, dtype, device)
+        self.dim = dim
+        self.device = self.store.device
+        self._pks: List[int] = []
+        self._doc: List[int] = []
+        self._text: List[Optional[str]] = []
+        self._order: List[int] = []
+        self._meta: Dict[str, List[Any]] = {}
+        self._cols: Dict[str, np.ndarray] = {}
+        self._row_of_pk: Dict[int, int] = {}
+        self.documents: Dict[int, Any] = {}
+
+    def __len__(self):
+        return len(self._pks)
+
+    def add(self, pks: Sequence[int], embeddings, document_ids: Optional[Sequence[int]] = None,
+            texts: Optional[Sequence[str]] = None, orders: Optional[Sequence[int]] = None, **meta) -> None:
+        """The write side: what ``bulk_update(rows, fields=['embedding'])`` does to the column
+        (assistant/processing/documents/steps/embeddings.py:35-39,65-69)."""
+        n = len(pks)
+        if n == 0:
+            return
+        emb = embeddings if isinstance(embeddings, torch.Tensor) else torch.as_tensor(np.asarray(embeddings, dtype=np.float32))
+        if emb.dim() != 2 or emb.shape[0] != n:
+            raise DabError(1, "embeddings must be [len(pks), dim]")
+        if emb.shape[1] != self.dim:
+            raise DabError(3, f"different vector dimensions {emb.shape[1]} and {self.dim}")
+        known = set(self._meta)
+        if len(self) and set(meta) != known:
+            raise DabError(1, f"filter columns changed: {sorted(meta)} vs {sorted(known)}")
+        self.store.append(emb.to(self.device))
+        base = len(self._pks)
+        for i, pk in enumerate(pks):
+            self._row_of_pk[int(pk)] = base + i
+        self._pks.extend(int(p) for p in pks)
+        self._doc.extend(int(d) for d in (document_ids if document_ids is not None else [0] * n))
+        self._text.extend(texts if texts is not None else [None] * n)
+        self._order.extend(int(o) for o in (orders if orders is not None else range(n)))
+        for k, v in meta.items():
+            self._meta.setdefault(k, []).extend(list(v))
+        self._cols.clear()
+
+    def column(self, name: str) -> np.ndarray:
+        if name not in self._cols:
+            if name in ("pk", "id"):
+                self._cols[name] = np.asarray(self._pks, dtype=np.int64)
+            elif name in ("document_id", "document__id", "document"):
+                self._cols[name] = np.asarray(self._doc, dtype=np.int64)
+            elif name == "order":
+                self._cols[name] = np.asarray(self._order, dtype=np.int64)
+            elif name in self._meta:
+                self._cols[name] = np.asarray(self._meta[name])
+            else:
+                raise DabError(1, f"unknown filter column {name!r}; known: pk, document_id, order, {sorted(self._meta)}")
+        return self._cols[name]
+
+    def bitmap_from_mask(self, mask: np.ndarray) -> torch.Tensor:
+        return ops.pack_allow_bitmap(torch.from_numpy(np.ascontiguousarray(mask, dtype=np.bool_)).to(self.device))
+
+    def bitmap_from_pks(self, pks: Iterable[int]) -> torch.Tensor:
+        mask = np.zeros(len(self), dtype=np.bool_)
+        rows = [self._row_of_pk[int(p)] for p in pks if int(p) in self._row_of_pk]
+        mask[rows] = True
+        return self.bitmap_from_mask(mask)
+
+    def search_rows(self, query_embeddings, n: int, bitmap: Optional[torch.Tensor] = None):
+        """(distances [Q, n'] float64 ascending, store rows [Q, n'] int64); n' <= n."""
+        q = torch.as_tensor(np.asarray(query_embeddings, dtype=np.float32))
+        if q.dim() == 1:
+            q = q[None]
+        if q.shape[-1] != self.dim:
+            raise DabError(3, f"different vector dimensions {q.shape[-1]} and {self.dim}")
+        if len(self) == 0 or n <= 0:
+            return np.zeros((q.shape[0], 0)), np.zeros((q.shape[0], 0), dtype=np.int64)
+        k = min(int(n), ops._lib.DAB_MAX_K)
+        scores, ids = self.store.search(q.to(self.device), k, bitmap)
+        scores, ids = scores.cpu().numpy().astype(np.float64), ids.cpu().numpy()
+        return 1.0 - scores, ids
+
+    def hits(self, dist_row: np.ndarray, rows_row: np.ndarray) -> List[ChunkRow]:
+        out = []
+        for d, r in zip(dist_row, rows_row):
+            if r < 0:
+                break  # fewer matching rows than n, like [:n] on a shorter queryset
+            out.append(ChunkRow(self._pks[r], self._doc[r], self._text[r], self._order[r], float(d)))
+        return out
+
+    def close(self):
+        self.store.close()
+
+
+_LOOKUPS = {
+    "exact": lambda c, v: c == v, "in": lambda c, v: np.isin(c, np.asarray(list(v))),
+    "lt": lambda c, v: c < v, "lte": lambda c, v: c <= v, "gt": lambda c, v: c > v, "gte": lambda c, v: c >= v,
+}
+
+
+class ChunkQuerySet:
+    """A filterable view over a ``DeviceTable`` - the part of Django's QuerySet the reference's
+    callers use before handing ``qs`` to the search (``.filter(...)`` with equality, ``__in`` and
+    comparison lookups; e.g. ``Question.objects.filter(document__wiki__bot=bot, ...)`` in
+    assistant/bot/services/context_service/steps/embeddings.py:26-29 and
+    ``filter(document__id__lt=...)`` in assistant/processing/documents/steps/questions.py:124)."""
+
+    def __init__(self, table: DeviceTable, mask: Optional[np.ndarray] = None):
+        self.table = table
+        self._mask = mask
+
+    def _apply(self, kwargs, negate: bool) -> "ChunkQuerySet":
+        mask = np.ones(len(self.table), dtype=np.bool_) if self._mask is None else self._mask.copy()
+        for key, value in kwargs.items():
+            name, op = key, "exact"
+            if "__" in key and key.rsplit("__", 1)[1] in _LOOKUPS:
+                name, op = key.rsplit("__", 1)
+            value = getattr(value, "pk", value)  # model instances compare by pk, like the ORM
+            hit = _LOOKUPS[op](self.table.column(name), value)
+            mask &= ~hit if negate else hit
+        return ChunkQuerySet(self.table, mask)
+
+    def filter(self, **kwargs) -> "ChunkQuerySet":
+        return self._apply(kwargs, False) if kwargs else ChunkQuerySet(self.table, self._mask)
+
+    def exclude(self, **kwargs) -> "ChunkQuerySet":
+        return self._apply(kwargs, True)
+
+    def all(self) -> "ChunkQuerySet":
+        return self
+
+    def count(self) -> int:
+        return len(self.table) if self._mask is None else int(self._mask.sum())
+
+    def allow_bitmap(self) -> Optional[torch.Tensor]:
+        return None if self._mask is None else self.table.bitmap_from_mask(self._mask)
+
+
+# --------------------------------------------------------------------------- registry / configuration
+_tables: Dict[Tuple[str, str], DeviceTable] = {}
+_embedder = None
+
+
+def register_table(model_label: str, field: str, table: DeviceTable) -> None:
+    """Make ``table`` the device copy of ``<model_label>.<field>`` (e.g. ``("storage.question",
+    "embedding")``) for searches that arrive with a Django queryset."""
+    _tables[(model_label.lower(), field)] = table
+
+
+def configure(embedder=None) -> None:
+    """Set the embedder ``get_embedding`` uses - the stand-in for
+    ``get_ai_embdedder(settings.EMBEDDING_AI_MODEL)`` (search_service.py:156-157)."""
+    global _embedder
+    _embedder = embedder
+
+
+def _table_and_bitmap(qs, field: str):
+    if isinstance(qs, ChunkQuerySet):
+        return qs.table, qs.allow_bitmap(), None
+    model = getattr(qs, "model", None)
+    if model is None:
+        raise DabError(1, "qs must be a ChunkQuerySet or a Django QuerySet")
+    label = getattr(getattr(model, "_meta", None), "label_lower", getattr(model, "__name__", "").lower())
+    table = _tables.get((label, field))
+    if table is None:
+        raise DabError(1, f"no device table registered for {label}.{field}")
+    pks = list(qs.values_list("pk", flat=True))
+    return table, table.bitmap_from_pks(pks), model
+
+
+def _search_sync(query_embedding, qs, n: int, field: str):
+    table, bitmap, model = _table_and_bitmap(qs, field)
+    dist, rows = table.search_rows(query_embedding, n, bitmap)
+    hits = table.hits(dist[0], rows[0])
+    if model is None:
+        return hits
+    objs = model.objects.in_bulk([h.pk for h in hits])
+    out = []
+    for h in hits:
+        o = objs.get(h.pk)
+        if o is not None:
+            o.distance = h.distance
+            out.append(o)
+    return out
+
+
+# --------------------------------------------------------------------------- the reference's API
+async def _objects_embedding_search(query_embedding: List[float], qs, n: int = 10, field: str = 'embedding') -> List[Any]:
+    """search_service.py:185-196: the top ``n`` objects of ``qs`` ordered by cosine distance to
+    ``query_embedding``, each with ``.distance`` (ascending).  The blocking device call runs in a
+    worker thread (the reference hops threads with ``sync_to_async``, :191)."""
+    return await asyncio.to_thread(_search_sync, query_embedding, qs, n, field)
+
+
+async def embedding_search_documents(query_embedding: List[float], qs, n: int = 10):
+    """search_service.py:161-166."""
+    return await _objects_embedding_search(query_embedding, qs, n, field='content_embedding')
+
+
+async def embedding_search_questions(query_embedding: List[float], qs, n: int = 10):
+    """search_service.py:169-174."""
+    return await _objects_embedding_search(query_embedding, qs, n)
+
+
+async def embedding_search_sentences(query_embedding: List[float], qs, n: int = 10):
+    """search_service.py:177-182."""
+    return await _objects_embedding_search(query_embedding, qs, n)
+
+
+def aggregate_documents(top_objects: Sequence[Any], max_scores_n: int, top_n: int) -> List[Tuple[int, float]]:
+    """search_service.py:133-150 without the ORM fetch: group hits by ``document_id`` in rank order,
+    keep documents with at least ``max_scores_n`` hits, score ``1 - mean(first max_scores_n
+    distances)``, best ``top_n``."""
+    docs = defaultdict(list)
+    for obj in top_objects:
+        docs[obj.document_id].append(obj)
+    doc_scores = {
+        doc_id: 1 - sum([o.distance for o in v[:max_scores_n]]) / max_scores_n
+        for doc_id, v in docs.items() if len(v) >= max_scores_n
+    }
+    result = sorted(doc_scores.items(), key=lambda x: x[1], reverse=True)
+    return result[:top_n]
+
+
+async def embedding_search(query: str, qs, max_scores_n: int = 10, top_n: int = 10) -> List[Tuple[Any, float]]:
+    """search_service.py:111-152: embed the query, take the ``max_scores_n * top_n * 10`` nearest
+    rows (:129-131), aggregate per document."""
+    logger.info(f'Embedding search for query: {query}')
+    query_embedding = await get_embedding(query)
+    top_objects = await _objects_embedding_search(query_embedding, qs, n=max_scores_n * top_n * 10)
+    scored = aggregate_documents(top_objects, max_scores_n, top_n)
+    if isinstance(qs, ChunkQuerySet):
+        lookup = qs.table.documents
+        return [(lookup.get(doc_id, doc_id), score) for doc_id, score in scored]
+    doc_model = qs.model._meta.get_field('document').related_model
+    found = {d.id: d for d in await asyncio.to_thread(
+        lambda: list(doc_model.objects.filter(id__in=[d for d, _ in scored])))}
+    return [(found[doc_id], score) for doc_id, score in scored if doc_id in found]
+
+
+async def get_embedding(text: str) -> List[float]:
+    """search_service.py:155-158."""
+    if _embedder is None:
+        raise DabError(1, "no embedder configured: call dab_b200.search_service.configure(embedder=...)")
+    return (await _embedder.embeddings([text]))[0]

@@ -1,0 +1,171 @@
+"""GPU tests of the drop-in Python surface: the reference's search_service / embedder API on the B200."""
+import asyncio
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pool_ref, search_ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture()
+def table():
+    from dab_b200.search_service import DeviceTable
+    rng = np.random.default_rng(42)
+    n, d = 3000, 768
+    emb = rng.standard_normal((n, d)).astype(np.float32)
+    pks = np.arange(1000, 1000 + n)                     # Django pks, ascending with insertion
+    docs = rng.integers(1, 60, size=n)
+    bots = docs % 3
+    t = DeviceTable(n, d, torch.float32, DEV)
+    t.add(pks[:1700], emb[:1700], document_ids=docs[:1700], texts=[f"q{i}" for i in range(1700)], document__wiki__bot=bots[:1700])
+    t.add(pks[1700:], emb[1700:], document_ids=docs[1700:], texts=[f"q{i}" for i in range(1700, n)], document__wiki__bot=bots[1700:])
+    t._test = dict(emb=emb, pks=pks, docs=docs, bots=bots)
+    yield t
+    t.close()
+
+
+def test_objects_embedding_search_matches_oracle(table):
+    """_objects_embedding_search (search_service.py:185-196): objects ordered by ascending distance,
+    filters honoured, fewer than n when the queryset is small."""
+    from dab_b200 import search_service as ss
+    T = table._test
+    q = np.random.default_rng(1).standard_normal(768).astype(np.float32)
+    S = search_ref.exact_scores(T["emb"], q)[0]
+    qs = ss.ChunkQuerySet(table)
+    hits = asyncio.run(ss._objects_embedding_search(q.tolist(), qs, n=5))
+    want, wsc = search_ref.rank_topk(S, 5)
+    assert [h.id for h in hits] == list(T["pks"][want])
+    np.testing.assert_allclose([h.distance for h in hits], 1 - wsc, atol=2e-6)
+    assert all(hits[i].distance <= hits[i + 1].distance for i in range(4))
+    assert hits[0].text == f"q{want[0]}" and hits[0].document_id == T["docs"][want[0]]
+    # the query-time filter of EmbeddingsStep (steps/embeddings.py:26-29) and of MergeQuestionsStep (questions.py:124)
+    fqs = qs.filter(document__wiki__bot=2).filter(document__id__lt=40)
+    allow = (T["bots"] == 2) & (T["docs"] < 40)
+    hits = asyncio.run(ss.embedding_search_questions(q.tolist(), fqs, n=250))
+    want, wsc = search_ref.rank_topk(S, 250, allow)
+    assert [h.id for h in hits] == list(T["pks"][want])
+    tiny = qs.filter(pk__in=[1000, 1005, 2999])
+    hits = asyncio.run(ss.embedding_search_sentences(q.tolist(), tiny, n=10))
+    assert len(hits) == 3 and {h.id for h in hits} == {1000, 1005, 2999}
+    with pytest.raises(Exception, match="different vector dimensions"):
+        asyncio.run(ss._objects_embedding_search([0.0] * 5, qs, n=5))
+
+
+def test_embedding_search_doc_level(table):
+    """embedding_search (search_service.py:111-152) == oracle aggregation over the oracle ranking."""
+    from dab_b200 import search_service as ss
+    T = table._test
+    qv = np.random.default_rng(2).standard_normal(768).astype(np.float32)
+
+    class Emb:
+        async def embeddings(self, texts):
+            return [qv.tolist() for _ in texts]
+
+    ss.configure(Emb())
+    got = asyncio.run(ss.embedding_search("how do I reset my password", ss.ChunkQuerySet(table), max_scores_n=5, top_n=5))
+    S = search_ref.exact_scores(T["emb"], qv)[0]
+    ids, sc = search_ref.rank_topk(S, 5 * 5 * 10)
+    want = search_ref.doc_level_scores(T["docs"][ids], 1 - sc, 5, 5)
+    assert [d for d, _ in got] == [d for d, _ in want]
+    np.testing.assert_allclose([s for _, s in got], [s for _, s in want], atol=1e-6)
+    ss.configure(None)
+
+
+def test_django_style_queryset_path(table):
+    """A duck-typed Django queryset: pks select the allow-set, instances come back via in_bulk with .distance."""
+    from dab_b200 import search_service as ss
+    T = table._test
+
+    class Obj:
+        def __init__(self, pk):
+            self.pk = self.id = pk
+
+    class Manager:
+        def in_bulk(self, ids):
+            return {i: Obj(i) for i in ids}
+
+    class Meta:
+        label_lower = "storage.question"
+
+    class Question:
+        _meta = Meta()
+        objects = Manager()
+
+    class QS:
+        model = Question
+
+        def __init__(self, pks):
+            self._pks = pks
+
+        def values_list(self, *a, **k):
+            return self._pks
+
+    ss.register_table("storage.Question", "embedding", table)
+    allowed = [int(p) for p in T["pks"][::7]]
+    q = np.random.default_rng(3).standard_normal(768).astype(np.float32)
+    hits = asyncio.run(ss._objects_embedding_search(q.tolist(), QS(allowed), n=10))
+    allow = np.zeros(len(T["pks"]), bool)
+    allow[::7] = True
+    want, wsc = search_ref.rank_topk(search_ref.exact_scores(T["emb"], q)[0], 10, allow)
+    assert [h.pk for h in hits] == list(T["pks"][want]) and isinstance(hits[0], Obj)
+    np.testing.assert_allclose([h.distance for h in hits], 1 - wsc, atol=2e-6)
+
+
+def _golden_model_and_tokenizer():
+    """Rebuilds exactly what oracle/make_golden.py fed the reference: same seed, same ids."""
+    from transformers import BatchEncoding, BertConfig, BertModel
+    torch.manual_seed(0)
+    cfg = BertConfig(vocab_size=30522, hidden_size=384, num_hidden_layers=2, num_attention_heads=12,
+                     intermediate_size=1536, max_position_embeddings=512)
+    model = BertModel(cfg).eval()
+    lengths = [5, 40, 17, 1, 33, 24]
+    rng = np.random.default_rng(20261106)
+    ids_per_text = {f"text-{i}": rng.integers(1000, 30000, size=L).astype(np.int64) for i, L in enumerate(lengths)}
+
+    def tokenizer(texts, return_tensors="pt", padding=True):
+        T = max(len(ids_per_text[t]) for t in texts)
+        ids = torch.zeros(len(texts), T, dtype=torch.long)
+        mask = torch.zeros(len(texts), T, dtype=torch.long)
+        for i, t in enumerate(texts):
+            L = len(ids_per_text[t])
+            ids[i, :L] = torch.from_numpy(ids_per_text[t])
+            mask[i, :L] = 1
+        return BatchEncoding({"input_ids": ids, "attention_mask": mask})
+
+    return model, tokenizer, list(ids_per_text)
+
+
+def test_b200_embedder_matches_reference_embedder(golden_dir):
+    """B200TransformersEmbedder.embeddings (batched, fused pool) vs the reference's
+    TransformersEmbedder.embeddings output recorded in tests/golden/pool_ref.npz."""
+    from dab_b200.embedders import B200TransformersEmbedder
+    g = np.load(os.path.join(golden_dir, "pool_ref.npz"))
+    model, tok, texts = _golden_model_and_tokenizer()
+    ref = g["ref_embeddings"]
+    emb = B200TransformersEmbedder("random-init-minilm-shaped", model=model, tokenizer=tok, device=DEV)
+    got = np.asarray(asyncio.run(emb.embeddings(texts)))
+    np.testing.assert_allclose(got, ref / np.linalg.norm(ref, axis=1, keepdims=True), rtol=1e-4, atol=5e-6)
+    raw = B200TransformersEmbedder("random-init-minilm-shaped", model=model, tokenizer=tok, device=DEV, unit_norm=False)
+    np.testing.assert_allclose(np.asarray(asyncio.run(raw.embeddings(texts))), ref, rtol=1e-4, atol=5e-6)
+    assert asyncio.run(emb.embeddings([])) == []
+
+
+def test_endpoint_with_b200_embedder():
+    from fastapi.testclient import TestClient
+    from dab_b200.embedders import B200TransformersEmbedder
+    from dab_b200.gpu_service import create_app
+    model, tok, texts = _golden_model_and_tokenizer()
+    app = create_app(embedders={"minilm": B200TransformersEmbedder("minilm", model=model, tokenizer=tok, device=DEV)})
+    with TestClient(app) as c:
+        r = c.post("/embeddings/", json={"model": "MiniLM", "texts": texts[:3]})
+        assert r.status_code == 200
+        e = np.asarray(r.json()["embeddings"])
+        assert e.shape == (3, 384)
+        np.testing.assert_allclose(np.linalg.norm(e, axis=1), 1.0, rtol=1e-5)
+        r = c.post("/embeddings/", json={"model": "minilm", "texts": ["not-in-the-stub-vocabulary"]})
+        assert r.status_code == 500        # tokenizer KeyError surfaces as HTTP 500 with str(e)
