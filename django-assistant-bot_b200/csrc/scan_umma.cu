@@ -108,13 +108,22 @@ __device__ __forceinline__ long long level_tile(const LevelPlan &plan, int lvl, 
 
 __global__ void __launch_bounds__(kThreads, 1)
 scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
-                 const uint32_t *__restrict__ allow, SearchScratch sc, int q0, int nq, int n_pad, int stages,
-                 int tmem_cols, const __grid_constant__ LevelPlan plan) {
+                 const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pad, int stages,
+                 int tmem_cols, int groups, const __grid_constant__ LevelPlan plan) {
     extern __shared__ unsigned char smem_raw[];
     const int lvl = sc.ctrl->cur_level;
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];
-    if ((long long)blockIdx.x >= ntiles) return;
+    // Query-slice groups: when the query block is too wide to stay resident in one SM's shared
+    // memory it is cut into `groups` slices of n_pad columns.  CTA b scores slice b % groups over
+    // the tile sequence b / groups: the `groups` CTAs of a sequence stream the same corpus tiles at
+    // the same time, so HBM still sees every byte once and the other reads are L2 hits.
+    const int slice = blockIdx.x % groups;
+    const int seq = blockIdx.x / groups;
+    const int num_seq = gridDim.x / groups;
+    if ((long long)seq >= ntiles) return;
+    const int q0 = q0_all + slice * n_pad;
+    const int nq = max(0, min(n_pad, nq_all - slice * n_pad));
 
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int num_kb = sv.dim / kBlockK;
@@ -153,17 +162,18 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_s;
-    const long long my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    const long long my_tiles = (ntiles - seq + num_seq - 1) / num_seq;
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer
         if (lane == 0) {
             mbar_arrive_expect_tx(b_full, (uint32_t)(num_kb * b_kb_bytes));
-            for (int kb = 0; kb < num_kb; kb++) tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kBlockK, 0, b_full);
+            for (int kb = 0; kb < num_kb; kb++)
+                tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kBlockK, slice * n_pad, b_full);
             int s = 0;
             uint32_t ph = 0;
             for (long long it = 0; it < my_tiles; it++) {
-                const long long t = level_tile(plan, lvl, blockIdx.x + it * gridDim.x);
+                const long long t = level_tile(plan, lvl, seq + it * num_seq);
                 const int row0 = (int)(t * kTileRows);
                 for (int kb = 0; kb < num_kb; kb++) {
                     mbar_wait_bounded(&empty[s], ph ^ 1u);
@@ -209,7 +219,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
         for (long long it = 0; it < my_tiles; it++) {
             const int a = (int)(it & 1);
             const uint32_t aph = (uint32_t)((it >> 1) & 1);
-            const long long t = level_tile(plan, lvl, blockIdx.x + it * gridDim.x);
+            const long long t = level_tile(plan, lvl, seq + it * num_seq);
             const long long row = t * kTileRows + wq * 32 + lane;
             const float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
             mbar_wait_bounded(&tmem_full[a], aph);
@@ -336,23 +346,30 @@ void umma_release_maps(void *) {}
 
 int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq, const LevelPlan &plan,
                      int num_sms, cudaStream_t st) {
-    UmmaPlan up;
-    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK || !plan_umma(sv.dim, nq, &up))
-        return fail(DAB_E_INVALID, "scan_umma: needs a bf16 store, dim % 64 == 0 and a query block that fits shared memory");
+    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK) return fail(DAB_E_INVALID, "scan_umma: needs a bf16 store with dim % 64 == 0");
     if (plan.tile_rows != kTileRows) return fail(DAB_E_INVALID, "scan_umma: level plan built for another tile size");
+    // one slice if the whole query block stays resident in shared memory, else `groups` equal slices
+    const int qpass = umma_queries_per_pass(sv.dim);
+    if (qpass <= 0 || nq < 1) return fail(DAB_E_INVALID, "scan_umma: query block does not fit shared memory");
+    const int groups = (nq + qpass - 1) / qpass;
+    const int per_slice = (nq + groups - 1) / groups;
+    UmmaPlan up;
+    if (!plan_umma(sv.dim, per_slice, &up) || groups * up.n_pad > 2 * DAB_MAX_QUERY_BATCH - q0 || groups > num_sms)
+        return fail(DAB_E_INVALID, "scan_umma: query block does not fit shared memory");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
     if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows)) return rc;
-    // B rows q0 .. q0+n_pad of the bf16 query copy; rows past the live queries hold stale data whose
-    // columns the epilogue ignores.  The buffer is 2*DAB_MAX_QUERY_BATCH rows long, so the box never leaves it.
+    // B = rows q0 .. of the bf16 query copy, n_pad rows per slice; rows past the live queries hold stale
+    // data whose columns the epilogue ignores.  The buffer is 2*DAB_MAX_QUERY_BATCH rows long.
     if (int rc = make_map(&tmap_q, sc.qsplit + (size_t)q0 * sv.dim, (uint64_t)(2 * DAB_MAX_QUERY_BATCH - q0), (uint64_t)sv.dim,
                           (uint32_t)up.n_pad))
         return rc;
     DAB_CUDA_OK(cudaFuncSetAttribute(scan_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)up.smem));
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
-    const int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
+    const long long seqs = max_tiles < num_sms / groups ? max_tiles : num_sms / groups;
+    const int grid = (int)seqs * groups;
     scan_umma_kernel<<<grid, kThreads, up.smem, st>>>(tmap_rows, tmap_q, sv, allow, sc, q0, nq, up.n_pad, up.stages, up.tmem_cols,
-                                                      plan);
+                                                      groups, plan);
     DAB_LAUNCH_OK();
     return DAB_OK;
 }

@@ -299,14 +299,14 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
         const int k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
         const LevelPlan plan = make_level_plan(sv.n, umma_tile_rows(), 4 * k < k_cap ? 4 * k : k_cap);
-        const int qpass = umma_queries_per_pass(sv.dim);
         *num_levels_out = plan.num_levels;
         if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st, first_chunk)) return rc;
         for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
-            for (int q0 = 0; q0 < nq; q0 += qpass) {
-                const int n_sub = nq - q0 < qpass ? nq - q0 : qpass;
+            {
+                // one launch scores all nq queries: slices of the query block run side by side on
+                // different SMs over the same tile stream (see scan_umma.cu)
                 ScanTimer tm(s->prof, st);
-                if (int rc = launch_scan_umma(sv, allow, sc, q0, n_sub, plan, s->num_sms, st)) return rc;
+                if (int rc = launch_scan_umma(sv, allow, sc, 0, nq, plan, s->num_sms, st)) return rc;
                 tm.stop();
             }
             if (int rc = launch_compact_margin(sc, nq, k, k_cap, margin, plan.num_levels, st)) return rc;
