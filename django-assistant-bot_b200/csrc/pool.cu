@@ -10,6 +10,7 @@
 // cluster's rank-0 CTA normalises and writes the row.  S is picked so that B*S covers
 // the 148 SMs a few times even for small batches.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -65,7 +66,14 @@ struct Vec<true> {  // 8 bf16 per 16 bytes
     }
 };
 
+constexpr int kTokChunk = 2048;  // tokens whose mask is compacted into shared memory at a time
+
 // NV = 16-byte column vectors per thread (1 when D*elem <= 4 KiB, up to 4).
+//
+// Per text: the mask is compacted, chunk by chunk, into a shared list of the token rows that count;
+// the S CTAs of the cluster and the row groups inside a CTA then take entries of that list round
+// robin.  Masked-out rows cost nothing (never loaded), work is balanced however ragged the batch
+// is, and no load waits on a mask load.
 template <bool BF16, int NV>
 __global__ void __launch_bounds__(kPoolThreads)
 pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ mask, int mask_dtype,
@@ -76,23 +84,21 @@ pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ ma
     extern __shared__ float smem[];
     float *part = smem;                                    // [row_groups][D] partial sums of this CTA
     float *psum = smem + (size_t)row_groups * D;           // [D] CTA total, read by rank 0 over DSMEM
+    __shared__ unsigned short s_rows[kTokChunk];           // compacted offsets (within the chunk) of counted tokens
+    __shared__ int s_warp_tot[kPoolThreads / 32];
     __shared__ float s_red[kPoolThreads / 32];
-    __shared__ int s_cnt[kPoolThreads / 32];
-    __shared__ int s_count;                                // unmasked tokens in this CTA's slice
     __shared__ float s_inv;
 
     cg::cluster_group cluster = cg::this_cluster();
     const int S = gridDim.x;
     const int rank = blockIdx.x;
     const long long b = blockIdx.y;
-    const int tid = threadIdx.x;
-    const int rg = tid / vecs_per_row * (NV == 1 ? 1 : 0);  // NV > 1 => one row group
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rg = NV == 1 ? tid / vecs_per_row : 0;       // NV > 1 => one row group
     const int c0 = NV == 1 ? tid % vecs_per_row : tid;
     const bool active = NV == 1 ? (tid < row_groups * vecs_per_row) : true;
-
-    const int per = (T + S - 1) / S;
-    const int t0 = rank * per;
-    const int t1 = min(T, t0 + per);
+    const int lanes_total = S * row_groups;                // list entries are dealt to (rank, row group) pairs
+    const int my_lane = rank * row_groups + rg;
 
     float acc[NV][VE];
 #pragma unroll
@@ -100,38 +106,68 @@ pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ ma
 #pragma unroll
         for (int e = 0; e < VE; e++) acc[v][e] = 0.f;
 
-    if (active) {
-        const uint4 *base = hidden + (size_t)b * T * vecs_per_row;
-        for (int t = t0 + rg; t < t1; t += row_groups * U) {
-            uint4 vals[U][NV];
-            bool on[U];
+    int total = 0;  // counted tokens of the whole text (every CTA of the cluster computes the same number)
+    const uint4 *base = hidden + (size_t)b * T * vecs_per_row;
+    for (int chunk0 = 0; chunk0 < T; chunk0 += kTokChunk) {
+        const int clen = min(kTokChunk, T - chunk0);
+        int n_c;
+        if (mask == nullptr) {
+            n_c = clen;
+        } else {
+            // ordered compaction of the chunk's mask: ballot + warp prefix + per-warp totals
+            n_c = 0;
+            for (int t0 = 0; t0 < clen; t0 += kPoolThreads) {
+                const int t = t0 + tid;
+                const bool on = t < clen && mask_on(mask, mask_dtype, b * T + chunk0 + t);
+                const unsigned bal = __ballot_sync(0xffffffffu, on);
+                if (lane == 0) s_warp_tot[warp] = __popc(bal);
+                __syncthreads();
+                int off = n_c, blk = 0;
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int tt = t + u * row_groups;
-                on[u] = tt < t1 && mask_on(mask, mask_dtype, b * T + tt);
+                for (int w = 0; w < kPoolThreads / 32; w++) {
+                    const int c = s_warp_tot[w];
+                    if (w < warp) off += c;
+                    blk += c;
+                }
+                if (on) s_rows[off + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)t;
+                n_c += blk;
+                __syncthreads();
             }
+        }
+        total += n_c;
+        if (active) {
+            for (int j = my_lane; j < n_c; j += lanes_total * U) {
+                uint4 vals[U][NV];
+                bool on[U];
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                if (on[u]) {
-                    const uint4 *row = base + (size_t)(t + u * row_groups) * vecs_per_row;
+                for (int u = 0; u < U; u++) {
+                    const int jj = j + u * lanes_total;
+                    on[u] = jj < n_c;
+                    if (on[u]) {
+                        const int t = chunk0 + (mask == nullptr ? jj : (int)s_rows[jj]);
+                        const uint4 *row = base + (size_t)t * vecs_per_row;
 #pragma unroll
-                    for (int v = 0; v < NV; v++) {
-                        const int c = c0 + v * kPoolThreads;
-                        if (NV == 1 || c < vecs_per_row) vals[u][v] = ld_stream(row + c);
+                        for (int v = 0; v < NV; v++) {
+                            const int c = c0 + v * kPoolThreads;
+                            if (NV == 1 || c < vecs_per_row) vals[u][v] = ld_stream(row + c);
+                        }
                     }
                 }
-            }
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                if (on[u]) {
+                for (int u = 0; u < U; u++) {
+                    if (on[u]) {
 #pragma unroll
-                    for (int v = 0; v < NV; v++) {
-                        const int c = c0 + v * kPoolThreads;
-                        if (NV == 1 || c < vecs_per_row) Vec<BF16>::add(acc[v], vals[u][v]);
+                        for (int v = 0; v < NV; v++) {
+                            const int c = c0 + v * kPoolThreads;
+                            if (NV == 1 || c < vecs_per_row) Vec<BF16>::add(acc[v], vals[u][v]);
+                        }
                     }
                 }
             }
         }
+        __syncthreads();  // s_rows is rewritten by the next chunk
+    }
+    if (active) {
 #pragma unroll
         for (int v = 0; v < NV; v++) {
             const int c = c0 + v * kPoolThreads;
@@ -141,28 +177,16 @@ pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ ma
             }
         }
     }
-    // token count of this slice
-    int cnt = 0;
-    for (int tt = t0 + tid; tt < t1; tt += kPoolThreads) cnt += mask_on(mask, mask_dtype, b * T + tt) ? 1 : 0;
-    cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if ((tid & 31) == 0) s_cnt[tid >> 5] = cnt;
     __syncthreads();
-    if (tid == 0) {
-        int c = 0;
-        for (int w = 0; w < kPoolThreads / 32; w++) c += s_cnt[w];
-        s_count = c;
-    }
     // fixed-order reduction over the row groups -> psum
     for (int d = tid; d < D; d += kPoolThreads) {
         float s = 0.f;
         for (int g = 0; g < row_groups; g++) s += part[(size_t)g * D + d];
         psum[d] = s;
     }
-    cluster.sync();  // every CTA's psum / s_count is visible cluster-wide
+    cluster.sync();  // every CTA's psum is visible cluster-wide
 
     if (rank == 0) {
-        int total = 0;
-        for (int r = 0; r < S; r++) total += *cluster.map_shared_rank(&s_count, r);
         const float inv_cnt = 1.0f / (float)max(total, 1);
         float ss = 0.f;
         for (int d = tid; d < D; d += kPoolThreads) {
@@ -173,7 +197,7 @@ pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ ma
             ss += s * s;
         }
         ss = warp_sum(ss);
-        if ((tid & 31) == 0) s_red[tid >> 5] = ss;
+        if (lane == 0) s_red[warp] = ss;
         __syncthreads();
         if (tid == 0) {
             float t = 0.f;
@@ -219,10 +243,14 @@ int launch_pool(const void *hidden, const void *mask, int mask_dtype, float *out
 
 }  // namespace
 
-// chosen so B*S fills the SMs ~3x when the batch is small, never slicing below 16 tokens per row group
+// chosen so B*S gives every SM several CTAs, never dealing fewer than ~16 tokens to a row group
 int pool_pick_splits(int64_t B, int64_t T, int row_groups) {
+    if (const char *e = getenv("DAB_POOL_SPLITS")) {  // tuning aid: force the cluster size (1, 2, 4, 8)
+        const int v = atoi(e);
+        if (v == 1 || v == 2 || v == 4 || v == 8) return v;
+    }
     int S = 1;
-    while (S < 8 && B * S < 3 * 148 && T / (2 * S) >= 16 * row_groups) S *= 2;
+    while (S < 8 && B * S < 4 * 148 && T / (2 * S) >= 16 * row_groups) S *= 2;
     return S;
 }
 
