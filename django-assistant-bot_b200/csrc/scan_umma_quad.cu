@@ -1,0 +1,334 @@
+// scan_umma_quad.cu - tensor-core scoring for WIDE query blocks (up to 256 queries in one corpus pass).
+//
+// Why a second kernel.  scan_umma.cu keeps the bf16 query block resident in one SM's shared memory,
+// which caps it at ~96 queries for dim 768; wider blocks had to be cut into slices that each re-read
+// the corpus tiles through L2, and L2 (~6.9 TB/s measured) is no faster than HBM on this chip.  Here a
+// thread-block CLUSTER of 4 CTAs shares ONE stream of corpus tiles:
+//
+//   * the query block is cut in two halves, one per CTA PAIR; inside a pair the two SMs run
+//     tcgen05.mma.cta_group::2 (M = 256 corpus rows, N = half the queries): each SM holds only a
+//     QUARTER of the query block in shared memory (98 KiB at dim 768, Q = 256) and 128 of the 256
+//     corpus rows of a super-tile; the accumulator halves live in the two SMs' TMEM;
+//   * both pairs need the same corpus rows, so the A tiles are loaded once per cluster and
+//     TMA-MULTICAST to the matching CTA of the other pair (cp.async.bulk.tensor ... .multicast::cluster,
+//     .cta_group::2 so that the byte counts land on the pair leader's mbarrier);
+//   * tcgen05.commit ... .multicast::cluster releases the shared-memory stage in the loading CTAs and
+//     publishes the accumulator to both CTAs of the pair; epilogue warps of all four CTAs drain
+//     their own TMEM half (threshold test, rare appends) while the next super-tile's MMAs run.
+//
+// HBM and L2 traffic = the corpus bytes, once per launch.  Roles per CTA (8 warps):
+//   warp 0 lane 0   TMA producer (A tiles: ranks 0 and 1 only; B quarter: every rank)
+//   warp 1 lane 0   MMA issuer (pair leaders = even ranks only)
+//   warp 2          TMEM allocator (cta_group::2, executed in both CTAs of a pair)
+//   warp 3 lane 0   tells the pair leader when this CTA's query quarter has landed
+//   warps 4-7       epilogue
+#include "umma.cuh"
+
+namespace dab {
+
+namespace {
+
+using namespace umma;
+constexpr int kThreads = 256;
+constexpr int kCluster = 4;
+constexpr int kMaxStages = 8;
+constexpr int kMinStages = 3;
+constexpr int kSuperRows = 2 * kTileRows;  // corpus rows per MMA pair step (UMMA M = 256)
+constexpr int kSmemBudget = 227 * 1024 - 2048;
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the pair bit of a shared::cluster address -> even CTA of the pair
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the mbarrier at the same offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+        ::"r"(smem_u32(bar)), "r"(rank)
+        : "memory");
+}
+// A-tile load, multicast to the CTAs in `mask`; complete_tx goes to the pair LEADER of every destination
+__device__ __forceinline__ void tma_load_2d_mc2(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%4, %5}], [%2], %3;"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "h"(mask), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t *smem_out, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_f16_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrive (once) on the mbarrier at this offset in every CTA of `mask` when the MMAs issued so far are done
+__device__ __forceinline__ void umma_commit_mc2(uint64_t *bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
+                      const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pair, int stages,
+                      int tmem_cols, const __grid_constant__ LevelPlan plan) {
+    extern __shared__ unsigned char smem_raw[];
+    const int lvl = sc.ctrl->cur_level;
+    if (lvl >= plan.num_levels) return;
+    const long long ntiles = plan.tiles_in_level[lvl];  // super-tiles of 256 rows
+    const int cluster_id = blockIdx.x / kCluster;
+    const int num_clusters = gridDim.x / kCluster;
+    if ((long long)cluster_id >= ntiles) return;       // same decision in all 4 CTAs of the cluster
+
+    const uint32_t rank = cluster_ctarank();
+    const int pair = (int)(rank >> 1), half = (int)(rank & 1);
+    const bool leader = half == 0;
+    const int n_half = n_pair / 2;                      // query rows of the B operand this CTA holds
+    const int q0 = q0_all + pair * n_pair;              // first query of this pair
+    const int nq = max(0, min(n_pair, nq_all - pair * n_pair));
+
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int num_kb = sv.dim / kBlockK;
+    const int b_kb_bytes = n_half * kBlockK * 2;
+    unsigned char *b_smem = smem;                                              // [num_kb][n_half rows x 128 B]
+    unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;              // [stages][128 rows x 128 B]
+    float *tau_s = reinterpret_cast<float *>(a_smem + (size_t)stages * kAStageBytes);  // [256]
+    uint64_t *full = reinterpret_cast<uint64_t *>(tau_s + DAB_MAX_QUERY_BATCH);        // leaders: both A halves landed
+    uint64_t *empty = full + kMaxStages;               // ranks 0/1: both pairs are done with the stage
+    uint64_t *b_full = empty + kMaxStages;             // this CTA's query quarter landed
+    uint64_t *b_pair = b_full + 1;                     // leaders: both quarters of the pair landed
+    uint64_t *tmem_full = b_pair + 1;                  // [2] accumulator stage complete (both CTAs of the pair)
+    uint64_t *tmem_empty = tmem_full + 2;              // [2] leaders: both CTAs drained the accumulator stage
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < stages; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 2);
+        }
+        mbar_init(b_full, 1);
+        mbar_init(b_pair, 2);
+        for (int a = 0; a < 2; a++) {
+            mbar_init(&tmem_full[a], 1);
+            mbar_init(&tmem_empty[a], 8);
+        }
+        fence_barrier_init();
+        prefetch_tmap(&tmap_rows);
+        prefetch_tmap(&tmap_q);
+    }
+    if (warp == 2) tmem_alloc2(tmem_base_s, (uint32_t)tmem_cols);
+    for (int q = tid; q < DAB_MAX_QUERY_BATCH; q += kThreads) {
+        const bool live = q < nq && sc.active[q0 + q];
+        tau_s[q] = live ? key_score(sc.tau_key[q0 + q]) : INFINITY;
+    }
+    tc_fence_before();
+    cluster_sync_all();   // barriers of every CTA are initialised before any remote arrive / multicast
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_s;
+    const long long my_tiles = (ntiles - cluster_id + num_clusters - 1) / num_clusters;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // this CTA's quarter of the query block: rows [pair*n_pair + half*n_half, +n_half) of the bf16 copy
+            mbar_arrive_expect_tx(b_full, (uint32_t)(num_kb * b_kb_bytes));
+            for (int kb = 0; kb < num_kb; kb++)
+                tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kBlockK, pair * n_pair + half * n_half, b_full);
+            if (rank < 2) {
+                // A tiles for the whole cluster: my 128-row half of every super-tile, multicast to my
+                // twin in the other pair
+                const uint16_t mask = (uint16_t)((1u << rank) | (1u << (rank + 2)));
+                int s = 0;
+                uint32_t ph = 0;
+                for (long long it = 0; it < my_tiles; it++) {
+                    const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
+                    const int row0 = (int)(t * kSuperRows) + half * kTileRows;
+                    for (int kb = 0; kb < num_kb; kb++) {
+                        mbar_wait_bounded(&empty[s], ph ^ 1u);
+                        tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s], mask);
+                        if (++s == stages) { s = 0; ph ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && leader) {
+            // ------------------------------------------------------------ MMA issuer of the pair
+            const uint32_t idesc = make_idesc(n_pair, kSuperRows);
+            const uint16_t pair_mask = (uint16_t)(0x3u << (2 * pair));
+            mbar_wait_bounded(b_pair, 0);
+            tc_fence_after();
+            int s = 0;
+            uint32_t ph = 0;
+            for (long long it = 0; it < my_tiles; it++) {
+                const int a = (int)(it & 1);
+                const uint32_t aph = (uint32_t)((it >> 1) & 1);
+                mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)(a * n_pair);
+                for (int kb = 0; kb < num_kb; kb++) {
+                    // both 16 KiB halves of the stage (mine and my peer's) report to this barrier
+                    mbar_arrive_expect_tx(&full[s], 2 * kAStageBytes);
+                    mbar_wait_bounded(&full[s], ph);
+                    tc_fence_after();
+                    const uint64_t da = make_smem_desc(smem_u32(a_smem + (size_t)s * kAStageBytes));
+                    const uint64_t db = make_smem_desc(smem_u32(b_smem + (size_t)kb * b_kb_bytes));
+#pragma unroll
+                    for (int k = 0; k < kBlockK / kUmmaK; k++)
+                        umma_f16_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_commit_mc2(&empty[s], (uint16_t)0x3u);        // the loaders are ranks 0 and 1
+                    if (++s == stages) { s = 0; ph ^= 1u; }
+                }
+                umma_commit_mc2(&tmem_full[a], pair_mask);
+            }
+        }
+    } else if (warp == 3) {
+        if (lane == 0) {
+            mbar_wait_bounded(b_full, 0);
+            if (leader) mbar_arrive(b_pair); else mbar_arrive_remote(b_pair, rank & ~1u);
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------ epilogue (own TMEM half)
+        const int wq = warp & 3;
+        for (long long it = 0; it < my_tiles; it++) {
+            const int a = (int)(it & 1);
+            const uint32_t aph = (uint32_t)((it >> 1) & 1);
+            const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
+            const long long row = t * kSuperRows + half * kTileRows + wq * 32 + lane;
+            const float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
+            mbar_wait_bounded(&tmem_full[a], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair);
+            for (int c0 = 0; c0 < nq; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(taddr + (uint32_t)c0, v);
+                tmem_ld_wait();
+                uint32_t pass = 0;
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) {
+                    const float4 tq = *reinterpret_cast<const float4 *>(tau_s + c0 + j);
+                    pass |= (__uint_as_float(v[j + 0]) * rinv >= tq.x ? 1u : 0u) << (j + 0);
+                    pass |= (__uint_as_float(v[j + 1]) * rinv >= tq.y ? 1u : 0u) << (j + 1);
+                    pass |= (__uint_as_float(v[j + 2]) * rinv >= tq.z ? 1u : 0u) << (j + 2);
+                    pass |= (__uint_as_float(v[j + 3]) * rinv >= tq.w ? 1u : 0u) << (j + 3);
+                }
+                if (pass) {
+                    const bool ok = rinv > 0.f && (allow == nullptr || ((allow[row >> 5] >> (row & 31)) & 1u));
+                    if (ok) {
+#pragma unroll
+                        for (int j = 0; j < 16; j++) {
+                            if (pass & (1u << j)) {
+                                const int q = q0 + c0 + j;
+                                const uint64_t key = make_key(__uint_as_float(v[j]) * rinv, (uint32_t)row);
+                                if (key > sc.tau_key[q]) {
+                                    const uint32_t pos = atomicAdd(&sc.cand_count[q], 1u);
+                                    if (pos < (uint32_t)kCandCap) sc.cand[(size_t)q * kCandCap + pos] = key;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (leader) mbar_arrive(&tmem_empty[a]); else mbar_arrive_remote(&tmem_empty[a], rank & ~1u);
+            }
+        }
+    }
+    // ---------------------------------------------------------------- teardown
+    tc_fence_before();
+    cluster_sync_all();   // nobody may free TMEM or leave while a peer still multicasts into / reads from it
+    if (warp == 2) tmem_dealloc2(tmem_base, (uint32_t)tmem_cols);
+}
+
+struct QuadPlan {
+    int n_pair;
+    int stages;
+    int tmem_cols;
+    size_t smem;
+};
+
+// n_pair = queries per CTA pair (multiple of 32: each CTA's B quarter must be a multiple of 16 rows)
+bool plan_quad(int dim, int nq, QuadPlan *out) {
+    int n_pair = ((nq + 1) / 2 + 31) / 32 * 32;
+    if (n_pair < 32) n_pair = 32;
+    if (n_pair > 128) return false;
+    const size_t b_bytes = (size_t)(n_pair / 2) * dim * 2;
+    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 8) * sizeof(uint64_t) + 1024;
+    if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
+    int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
+    if (stages > kMaxStages) stages = kMaxStages;
+    int cols = 32;
+    while (cols < 2 * n_pair) cols <<= 1;
+    out->n_pair = n_pair;
+    out->stages = stages;
+    out->tmem_cols = cols;
+    out->smem = b_bytes + (size_t)stages * kAStageBytes + fixed;
+    return true;
+}
+
+}  // namespace
+
+int quad_tile_rows() { return kSuperRows; }
+
+bool quad_supported(int dim, int dtype, int nq) {
+    QuadPlan p;
+    return dtype == DAB_BF16 && dim % kBlockK == 0 && nq >= 1 && nq <= DAB_MAX_QUERY_BATCH && plan_quad(dim, nq, &p);
+}
+
+int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
+                          const LevelPlan &plan, int num_sms, cudaStream_t st) {
+    QuadPlan qp;
+    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK || !plan_quad(sv.dim, nq, &qp))
+        return fail(DAB_E_INVALID, "scan_umma_quad: needs a bf16 store, dim % 64 == 0 and <= 256 queries that fit shared memory");
+    if (plan.tile_rows != kSuperRows) return fail(DAB_E_INVALID, "scan_umma_quad: level plan built for another tile size");
+    alignas(64) CUtensorMap tmap_rows, tmap_q;
+    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows)) return rc;
+    if (int rc = make_map(&tmap_q, sc.qsplit + (size_t)q0 * sv.dim, (uint64_t)(2 * DAB_MAX_QUERY_BATCH - q0), (uint64_t)sv.dim,
+                          (uint32_t)(qp.n_pair / 2)))
+        return rc;
+    DAB_CUDA_OK(cudaFuncSetAttribute(scan_umma_quad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qp.smem));
+    // how many 4-CTA clusters can be resident at once (GPC shapes strand a few SMs)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(num_sms / kCluster * kCluster), 1, 1);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = qp.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int max_clusters = 0;
+    DAB_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_clusters, scan_umma_quad_kernel, &cfg));
+    if (max_clusters < 1) return fail(DAB_E_CUDA, "scan_umma_quad: no 4-CTA cluster fits on this device");
+    long long max_tiles = 0;
+    for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
+    const long long clusters = max_tiles < max_clusters ? max_tiles : max_clusters;
+    cfg.gridDim = dim3((unsigned)(clusters * kCluster), 1, 1);
+    DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, scan_umma_quad_kernel, tmap_rows, tmap_q, sv, allow, sc, q0, nq, qp.n_pair, qp.stages,
+                                   qp.tmem_cols, plan));
+    count_launch();
+    return DAB_OK;
+}
+
+}  // namespace dab

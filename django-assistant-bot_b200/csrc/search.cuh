@@ -59,4 +59,11 @@ int umma_queries_per_pass(int dim);
 int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
                      const LevelPlan &plan, int num_sms, cudaStream_t st);
 
+
+// wide query blocks (up to 256): 4-CTA clusters, cta_group::2 MMA pairs, multicast corpus tiles
+int quad_tile_rows();
+bool quad_supported(int dim, int dtype, int nq);
+int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
+                          const LevelPlan &plan, int num_sms, cudaStream_t st);
+
 }  // namespace dab

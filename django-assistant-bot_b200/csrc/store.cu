@@ -5,6 +5,8 @@
 // bf16), 1/|row| per row, the row ids (Django pks), and the scratch a search needs.
 // dab_store_search is what `_objects_embedding_search` (assistant/rag/services/
 // search_service.py:185-196) becomes: exact cosine top-k, (score desc, row asc).
+#include <stdlib.h>
+
 #include <atomic>
 #include <mutex>
 #include <new>
@@ -298,15 +300,19 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
         const float margin = 2.0f * eps;
         const int k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
-        const LevelPlan plan = make_level_plan(sv.n, umma_tile_rows(), 4 * k < k_cap ? 4 * k : k_cap);
+        // wide blocks that do not fit one SM's shared memory go to the 4-CTA cluster kernel
+        static const bool no_quad = getenv("DAB_NO_QUAD") != nullptr;  // tuning aid: use query-slice groups instead
+        const bool quad = !no_quad && nq > umma_queries_per_pass(sv.dim) && quad_supported(sv.dim, sv.dtype, nq);
+        const LevelPlan plan = make_level_plan(sv.n, quad ? quad_tile_rows() : umma_tile_rows(), 4 * k < k_cap ? 4 * k : k_cap);
         *num_levels_out = plan.num_levels;
         if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st, first_chunk)) return rc;
         for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
             {
-                // one launch scores all nq queries: slices of the query block run side by side on
-                // different SMs over the same tile stream (see scan_umma.cu)
+                // one launch scores all nq queries
                 ScanTimer tm(s->prof, st);
-                if (int rc = launch_scan_umma(sv, allow, sc, 0, nq, plan, s->num_sms, st)) return rc;
+                if (int rc = quad ? launch_scan_umma_quad(sv, allow, sc, 0, nq, plan, s->num_sms, st)
+                                  : launch_scan_umma(sv, allow, sc, 0, nq, plan, s->num_sms, st))
+                    return rc;
                 tm.stop();
             }
             if (int rc = launch_compact_margin(sc, nq, k, k_cap, margin, plan.num_levels, st)) return rc;

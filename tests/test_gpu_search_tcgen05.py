@@ -41,6 +41,14 @@ def test_tcgen05_parity(N, D, Q, k):
     _run(N, D, Q, k, seed=N + D + Q + k)
 
 
+@pytest.mark.parametrize("N,D,Q,k", [(100_000, 768, 256, 100), (50_000, 1024, 256, 10), (20_000, 768, 100, 10),
+                                     (300, 768, 256, 5), (70_001, 768, 129, 50), (30_000, 384, 255, 10)])
+def test_tcgen05_wide_query_blocks_cluster_kernel(N, D, Q, k):
+    """More queries than fit one SM's shared memory: the 4-CTA cluster kernel (cta_group::2 pairs,
+    multicast corpus tiles) scores the whole block in one corpus pass."""
+    _run(N, D, Q, k, seed=N + D + Q + k)
+
+
 def test_tcgen05_dense_score_cluster_and_zero_row():
     _run(80_000, 768, 8, 50, seed=77, planted=True)
 
