@@ -140,48 +140,24 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     } else if (warp >= 4) {
         // ------------------------------------------------------------ epilogue
         const int wq = warp & 3;                               // TMEM lane quarter this warp may read
+        // the row's 1/|row| for the NEXT tile is fetched while the current one is drained
+        auto row_of = [&](long long it_) {
+            const long long t = level_tile(plan, lvl, seq + it_ * num_seq);
+            return t * kTileRows + wq * 32 + lane;
+        };
+        long long row = row_of(0);
+        float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
         for (long long it = 0; it < my_tiles; it++) {
             const int a = (int)(it & 1);
             const uint32_t aph = (uint32_t)((it >> 1) & 1);
-            const long long t = level_tile(plan, lvl, seq + it * num_seq);
-            const long long row = t * kTileRows + wq * 32 + lane;
-            const float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
+            const long long row_next = it + 1 < my_tiles ? row_of(it + 1) : sv.n;
+            const float rinv_next = row_next < sv.n ? sv.inv_norm[row_next] : 0.f;
             mbar_wait_bounded(&tmem_full[a], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pad);
-            for (int c0 = 0; c0 < n_pad; c0 += 16) {
-                uint32_t v[16];
-                tmem_ld16(taddr + (uint32_t)c0, v);
-                tmem_ld_wait();
-                if (c0 < nq) {
-                    uint32_t pass = 0;
-#pragma unroll
-                    for (int j = 0; j < 16; j += 4) {
-                        const float4 tq = *reinterpret_cast<const float4 *>(tau_s + c0 + j);
-                        pass |= (__uint_as_float(v[j + 0]) * rinv >= tq.x ? 1u : 0u) << (j + 0);
-                        pass |= (__uint_as_float(v[j + 1]) * rinv >= tq.y ? 1u : 0u) << (j + 1);
-                        pass |= (__uint_as_float(v[j + 2]) * rinv >= tq.z ? 1u : 0u) << (j + 2);
-                        pass |= (__uint_as_float(v[j + 3]) * rinv >= tq.w ? 1u : 0u) << (j + 3);
-                    }
-                    if (pass) {
-                        // slow path (rare once thresholds exist): exact key test, filter, append
-                        const bool ok = rinv > 0.f && (allow == nullptr || ((allow[row >> 5] >> (row & 31)) & 1u));
-                        if (ok) {
-#pragma unroll
-                            for (int j = 0; j < 16; j++) {
-                                if (pass & (1u << j)) {
-                                    const int q = q0 + c0 + j;
-                                    const uint64_t key = make_key(__uint_as_float(v[j]) * rinv, (uint32_t)row);
-                                    if (key > sc.tau_key[q]) {
-                                        const uint32_t pos = atomicAdd(&sc.cand_count[q], 1u);
-                                        if (pos < (uint32_t)kCandCap) sc.cand[(size_t)q * kCandCap + pos] = key;
-                                    }
-                                }
-                            }
-                        }
-                    }
-                }
-            }
+            epilogue_tile(taddr, (nq + 15) & ~15, rinv, row, tau_s, q0, allow, sc);
+            row = row_next;
+            rinv = rinv_next;
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[a]);

@@ -22,6 +22,9 @@
 //   warp 2          TMEM allocator (cta_group::2, executed in both CTAs of a pair)
 //   warp 3 lane 0   tells the pair leader when this CTA's query quarter has landed
 //   warps 4-7       epilogue
+#include <stdio.h>
+#include <stdlib.h>
+
 #include "umma.cuh"
 
 namespace dab {
@@ -33,6 +36,8 @@ constexpr int kThreads = 256;
 constexpr int kCluster = 4;
 constexpr int kMaxStages = 8;
 constexpr int kMinStages = 3;
+constexpr int kPendCap = 512;       // staged candidates per accumulator stage per CTA
+constexpr int kPrefetchAhead = 3;   // super-tiles kept ahead in L2 by each loading CTA
 constexpr int kSuperRows = 2 * kTileRows;  // corpus rows per MMA pair step (UMMA M = 256)
 constexpr int kSmemBudget = 227 * 1024 - 2048;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the pair bit of a shared::cluster address -> even CTA of the pair
@@ -61,6 +66,10 @@ __device__ __forceinline__ void tma_load_2d_mc2(void *smem_dst, const CUtensorMa
         " [%0], [%1, {%4, %5}], [%2], %3;"
         ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "h"(mask), "r"(c0), "r"(c1)
         : "memory");
+}
+// pull `bytes` (multiple of 16) at `gptr` into L2; fire and forget
+__device__ __forceinline__ void l2_prefetch(const void *gptr, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc2(uint32_t *smem_out, uint32_t cols) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)), "r"(cols) : "memory");
@@ -115,7 +124,12 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     uint64_t *b_pair = b_full + 1;                     // leaders: both quarters of the pair landed
     uint64_t *tmem_full = b_pair + 1;                  // [2] accumulator stage complete (both CTAs of the pair)
     uint64_t *tmem_empty = tmem_full + 2;              // [2] leaders: both CTAs drained the accumulator stage
-    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+    uint64_t *pend_full = tmem_empty + 2;              // [2] all 4 epilogue warps finished appending to list a
+    uint64_t *pend_free = pend_full + 2;               // [2] the flusher drained list a
+    uint64_t *pend_key = pend_free + 2;                // [2][kPendCap]
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(pend_key + 2 * kPendCap);
+    uint32_t *pend_n = tmem_base_s + 1;                // [2]
+    uint32_t *pend_q = pend_n + 2;                     // [2][kPendCap]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -128,6 +142,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         for (int a = 0; a < 2; a++) {
             mbar_init(&tmem_full[a], 1);
             mbar_init(&tmem_empty[a], 8);
+            mbar_init(&pend_full[a], 4);
+            mbar_init(&pend_free[a], 1);
+            pend_n[a] = 0;
         }
         fence_barrier_init();
         prefetch_tmap(&tmap_rows);
@@ -156,9 +173,24 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                 const uint16_t mask = (uint16_t)((1u << rank) | (1u << (rank + 2)));
                 int s = 0;
                 uint32_t ph = 0;
+                // Shared memory only holds ~7 x 16 KiB of loads in flight per loading CTA - not enough to
+                // cover HBM latency for a whole cluster.  So the rows of the super-tiles kPrefetchAhead
+                // steps ahead are pulled into L2 with a bulk prefetch (no shared memory, no barrier); the
+                // TMA loads that follow then hit L2.
+                const size_t row_bytes = (size_t)sv.dim * 2;
+                auto prefetch_half = [&](long long it_pf) {
+                    if (it_pf >= my_tiles) return;
+                    const long long tp = level_tile(plan, lvl, cluster_id + it_pf * num_clusters);
+                    const long long r0 = tp * kSuperRows + half * kTileRows;
+                    if (r0 >= sv.n) return;
+                    const long long nrows = min((long long)kTileRows, sv.n - r0);
+                    l2_prefetch(static_cast<const unsigned char *>(sv.rows) + (size_t)r0 * row_bytes, (uint32_t)(nrows * row_bytes));
+                };
+                for (int i = 0; i < kPrefetchAhead; i++) prefetch_half(i);
                 for (long long it = 0; it < my_tiles; it++) {
                     const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
                     const int row0 = (int)(t * kSuperRows) + half * kTileRows;
+                    prefetch_half(it + kPrefetchAhead);
                     for (int kb = 0; kb < num_kb; kb++) {
                         mbar_wait_bounded(&empty[s], ph ^ 1u);
                         tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s], mask);
@@ -203,52 +235,48 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             mbar_wait_bounded(b_full, 0);
             if (leader) mbar_arrive(b_pair); else mbar_arrive_remote(b_pair, rank & ~1u);
         }
-    } else if (warp >= 4) {
-        // ------------------------------------------------------------ epilogue (own TMEM half)
-        const int wq = warp & 3;
+        // ------------------------------------------------------------ flusher: staged candidates -> global buffers
         for (long long it = 0; it < my_tiles; it++) {
             const int a = (int)(it & 1);
             const uint32_t aph = (uint32_t)((it >> 1) & 1);
-            const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
-            const long long row = t * kSuperRows + half * kTileRows + wq * 32 + lane;
-            const float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
+            mbar_wait_bounded(&pend_full[a], aph);
+            const uint32_t n = min(pend_n[a], (uint32_t)kPendCap);
+            for (uint32_t i = lane; i < n; i += 32)
+                append_candidate(sc, allow, (int)pend_q[a * kPendCap + i], pend_key[a * kPendCap + i]);
+            __syncwarp();
+            if (lane == 0) {
+                pend_n[a] = 0;
+                mbar_arrive(&pend_free[a]);
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------ epilogue (own TMEM half)
+        const int wq = warp & 3;
+        // the row's 1/|row| for the NEXT tile is fetched while the current one is drained
+        auto row_of = [&](long long it_) {
+            const long long t = level_tile(plan, lvl, cluster_id + it_ * num_clusters);
+            return t * kSuperRows + half * kTileRows + wq * 32 + lane;
+        };
+        long long row = row_of(0);
+        float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
+        for (long long it = 0; it < my_tiles; it++) {
+            const int a = (int)(it & 1);
+            const uint32_t aph = (uint32_t)((it >> 1) & 1);
+            const long long row_next = it + 1 < my_tiles ? row_of(it + 1) : sv.n;
+            const float rinv_next = row_next < sv.n ? sv.inv_norm[row_next] : 0.f;
+            mbar_wait_bounded(&pend_free[a], aph ^ 1u);       // the flusher is done with list a (tile it-2)
             mbar_wait_bounded(&tmem_full[a], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair);
-            for (int c0 = 0; c0 < nq; c0 += 16) {
-                uint32_t v[16];
-                tmem_ld16(taddr + (uint32_t)c0, v);
-                tmem_ld_wait();
-                uint32_t pass = 0;
-#pragma unroll
-                for (int j = 0; j < 16; j += 4) {
-                    const float4 tq = *reinterpret_cast<const float4 *>(tau_s + c0 + j);
-                    pass |= (__uint_as_float(v[j + 0]) * rinv >= tq.x ? 1u : 0u) << (j + 0);
-                    pass |= (__uint_as_float(v[j + 1]) * rinv >= tq.y ? 1u : 0u) << (j + 1);
-                    pass |= (__uint_as_float(v[j + 2]) * rinv >= tq.z ? 1u : 0u) << (j + 2);
-                    pass |= (__uint_as_float(v[j + 3]) * rinv >= tq.w ? 1u : 0u) << (j + 3);
-                }
-                if (pass) {
-                    const bool ok = rinv > 0.f && (allow == nullptr || ((allow[row >> 5] >> (row & 31)) & 1u));
-                    if (ok) {
-#pragma unroll
-                        for (int j = 0; j < 16; j++) {
-                            if (pass & (1u << j)) {
-                                const int q = q0 + c0 + j;
-                                const uint64_t key = make_key(__uint_as_float(v[j]) * rinv, (uint32_t)row);
-                                if (key > sc.tau_key[q]) {
-                                    const uint32_t pos = atomicAdd(&sc.cand_count[q], 1u);
-                                    if (pos < (uint32_t)kCandCap) sc.cand[(size_t)q * kCandCap + pos] = key;
-                                }
-                            }
-                        }
-                    }
-                }
-            }
+            const PendList pend = {pend_key + a * kPendCap, pend_q + a * kPendCap, pend_n + a, kPendCap};
+            epilogue_tile(taddr, (nq + 15) & ~15, rinv, row, tau_s, q0, allow, sc, &pend);
+            row = row_next;
+            rinv = rinv_next;
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
                 if (leader) mbar_arrive(&tmem_empty[a]); else mbar_arrive_remote(&tmem_empty[a], rank & ~1u);
+                mbar_arrive(&pend_full[a]);
             }
         }
     }
@@ -271,7 +299,8 @@ bool plan_quad(int dim, int nq, QuadPlan *out) {
     if (n_pair < 32) n_pair = 32;
     if (n_pair > 128) return false;
     const size_t b_bytes = (size_t)(n_pair / 2) * dim * 2;
-    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 8) * sizeof(uint64_t) + 1024;
+    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 12) * sizeof(uint64_t) + 16 +
+                         2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
     int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
     if (stages > kMaxStages) stages = kMaxStages;
@@ -324,6 +353,10 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long clusters = max_tiles < max_clusters ? max_tiles : max_clusters;
+    static const bool debug = getenv("DAB_DEBUG") != nullptr;
+    if (debug)
+        fprintf(stderr, "[dab] quad: nq=%d n_pair=%d stages=%d tmem_cols=%d smem=%zu max_clusters=%d clusters=%lld levels=%d\n", nq,
+                qp.n_pair, qp.stages, qp.tmem_cols, qp.smem, max_clusters, clusters, plan.num_levels);
     cfg.gridDim = dim3((unsigned)(clusters * kCluster), 1, 1);
     DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, scan_umma_quad_kernel, tmap_rows, tmap_q, sv, allow, sc, q0, nq, qp.n_pair, qp.stages,
                                    qp.tmem_cols, plan));
