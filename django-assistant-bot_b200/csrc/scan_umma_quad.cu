@@ -37,7 +37,6 @@ constexpr int kCluster = 4;
 constexpr int kMaxStages = 8;
 constexpr int kMinStages = 3;
 constexpr int kPendCap = 512;       // staged candidates per accumulator stage per CTA
-constexpr int kPrefetchAhead = 3;   // super-tiles kept ahead in L2 by each loading CTA
 constexpr int kSuperRows = 2 * kTileRows;  // corpus rows per MMA pair step (UMMA M = 256)
 constexpr int kSmemBudget = 227 * 1024 - 2048;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the pair bit of a shared::cluster address -> even CTA of the pair
@@ -66,10 +65,6 @@ __device__ __forceinline__ void tma_load_2d_mc2(void *smem_dst, const CUtensorMa
         " [%0], [%1, {%4, %5}], [%2], %3;"
         ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "h"(mask), "r"(c0), "r"(c1)
         : "memory");
-}
-// pull `bytes` (multiple of 16) at `gptr` into L2; fire and forget
-__device__ __forceinline__ void l2_prefetch(const void *gptr, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc2(uint32_t *smem_out, uint32_t cols) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)), "r"(cols) : "memory");
@@ -173,24 +168,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                 const uint16_t mask = (uint16_t)((1u << rank) | (1u << (rank + 2)));
                 int s = 0;
                 uint32_t ph = 0;
-                // Shared memory only holds ~7 x 16 KiB of loads in flight per loading CTA - not enough to
-                // cover HBM latency for a whole cluster.  So the rows of the super-tiles kPrefetchAhead
-                // steps ahead are pulled into L2 with a bulk prefetch (no shared memory, no barrier); the
-                // TMA loads that follow then hit L2.
-                const size_t row_bytes = (size_t)sv.dim * 2;
-                auto prefetch_half = [&](long long it_pf) {
-                    if (it_pf >= my_tiles) return;
-                    const long long tp = level_tile(plan, lvl, cluster_id + it_pf * num_clusters);
-                    const long long r0 = tp * kSuperRows + half * kTileRows;
-                    if (r0 >= sv.n) return;
-                    const long long nrows = min((long long)kTileRows, sv.n - r0);
-                    l2_prefetch(static_cast<const unsigned char *>(sv.rows) + (size_t)r0 * row_bytes, (uint32_t)(nrows * row_bytes));
-                };
-                for (int i = 0; i < kPrefetchAhead; i++) prefetch_half(i);
                 for (long long it = 0; it < my_tiles; it++) {
                     const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
                     const int row0 = (int)(t * kSuperRows) + half * kTileRows;
-                    prefetch_half(it + kPrefetchAhead);
                     for (int kb = 0; kb < num_kb; kb++) {
                         mbar_wait_bounded(&empty[s], ph ^ 1u);
                         tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s], mask);

@@ -286,42 +286,63 @@ struct ScanTimer {
 };
 
 // The rounds of one query chunk (<= 256 queries), all enqueued on `st` without a host sync.
-int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc, const float *q_dev, int nq, int k,
-                     const uint32_t *allow, float *out_scores, int64_t *out_ids, int *num_levels_out, cudaStream_t st,
-                     bool first_chunk) {
-    int path = s->path;
-    if (path == 0) path = (umma_supported(sv.dim, sv.dtype) && nq > simt_queries_per_pass(sv.dim, sv.dtype)) ? 2 : 1;
-    if (path == 2) {
+// Everything a search of nq queries / top-k over n rows decides before launching anything.
+struct SearchPlan {
+    int path;        // 1 = CUDA cores, 2 = tcgen05
+    bool quad;       // tcgen05: 4-CTA cluster kernel for wide query blocks
+    int k_cap;       // candidates kept per query between levels
+    float margin;    // tensor path: approximate-score margin that is kept for rescoring
+    LevelPlan levels;
+};
+
+SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq, int k) {
+    SearchPlan sp = {};
+    sp.path = s->path;
+    if (sp.path == 0) sp.path = (umma_supported(dim, dtype) && nq > simt_queries_per_pass(dim, dtype)) ? 2 : 1;
+    if (sp.path == 2) {
         // Tensor path.  The pass scores with the query rounded to bf16: per element |dq| <= 2^-8 |q|, so by
         // Cauchy-Schwarz |approx - exact| <= 2^-8 for unit vectors, plus fp32 accumulation noise
         // (<= dim * 2^-24).  Everything within twice that bound of the k-th best approximate score
-        // can still belong to the exact top-k: it is kept (up to kKeepCap) and rescored in fp32.
-        const float eps = 0.00390625f + (float)sv.dim * 6e-8f;
-        const float margin = 2.0f * eps;
-        const int k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
-        // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
+        // can still belong to the exact top-k: it is kept (up to k_cap) and rescored in fp32.
+        const float eps = 0.00390625f + (float)dim * 6e-8f;
+        sp.margin = 2.0f * eps;
+        sp.k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // wide blocks that do not fit one SM's shared memory go to the 4-CTA cluster kernel
         static const bool no_quad = getenv("DAB_NO_QUAD") != nullptr;  // tuning aid: use query-slice groups instead
-        const bool quad = !no_quad && nq > umma_queries_per_pass(sv.dim) && quad_supported(sv.dim, sv.dtype, nq);
-        const LevelPlan plan = make_level_plan(sv.n, quad ? quad_tile_rows() : umma_tile_rows(), 4 * k < k_cap ? 4 * k : k_cap);
-        *num_levels_out = plan.num_levels;
+        sp.quad = !no_quad && nq > umma_queries_per_pass(dim) && quad_supported(dim, dtype, nq);
+        // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
+        sp.levels = make_level_plan(n, sp.quad ? quad_tile_rows() : umma_tile_rows(), 4 * k < sp.k_cap ? 4 * k : sp.k_cap);
+    } else {
+        sp.margin = 0.f;
+        sp.k_cap = k;
+        sp.levels = make_level_plan(n, simt_tile_rows(dim, dtype), k);
+    }
+    return sp;
+}
+
+// The rounds of one query chunk (<= 256 queries), all enqueued on `st` without a host sync.
+int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc, const float *q_dev, int nq, int k,
+                     const uint32_t *allow, float *out_scores, int64_t *out_ids, int *num_levels_out, cudaStream_t st,
+                     bool first_chunk) {
+    const SearchPlan sp = choose_plan(s, sv.n, sv.dim, sv.dtype, nq, k);
+    const LevelPlan &plan = sp.levels;
+    *num_levels_out = plan.num_levels;
+    if (sp.path == 2) {
         if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st, first_chunk)) return rc;
         for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
             {
                 // one launch scores all nq queries
                 ScanTimer tm(s->prof, st);
-                if (int rc = quad ? launch_scan_umma_quad(sv, allow, sc, 0, nq, plan, s->num_sms, st)
-                                  : launch_scan_umma(sv, allow, sc, 0, nq, plan, s->num_sms, st))
+                if (int rc = sp.quad ? launch_scan_umma_quad(sv, allow, sc, 0, nq, plan, s->num_sms, st)
+                                     : launch_scan_umma(sv, allow, sc, 0, nq, plan, s->num_sms, st))
                     return rc;
                 tm.stop();
             }
-            if (int rc = launch_compact_margin(sc, nq, k, k_cap, margin, plan.num_levels, st)) return rc;
+            if (int rc = launch_compact_margin(sc, nq, k, sp.k_cap, sp.margin, plan.num_levels, st)) return rc;
         }
-        return launch_finish_rescore(sc, sv, nq, k, k_cap, plan.num_levels, out_scores, out_ids, st);
+        return launch_finish_rescore(sc, sv, nq, k, sp.k_cap, plan.num_levels, out_scores, out_ids, st);
     }
     const int qb = simt_queries_per_pass(sv.dim, sv.dtype);
-    const LevelPlan plan = make_level_plan(sv.n, simt_tile_rows(sv.dim, sv.dtype), k);
-    *num_levels_out = plan.num_levels;
     if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, false, st, first_chunk)) return rc;
     for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
         for (int q0 = 0; q0 < nq; q0 += qb) {
@@ -433,5 +454,21 @@ extern "C" DAB_API int dab_store_get_profile(dab_store *s, float *scan_ms, int *
     };
     drain(s->prof.scan_events, scan_ms, scan_launches);
     drain(s->prof.search_events, search_ms, searches);
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *path, int *tile_rows, int *num_levels, int *growth,
+                                               int *strides /* [8] */) {
+    if (int rc = check_store(s, "dab_store_describe_plan")) return rc;
+    if (Q < 1 || k < 1 || k > DAB_MAX_K) return fail(DAB_E_INVALID, "dab_store_describe_plan: bad Q or k");
+    std::lock_guard<std::mutex> g(s->mu);
+    const int nq = Q < DAB_MAX_QUERY_BATCH ? Q : DAB_MAX_QUERY_BATCH;
+    const SearchPlan sp = choose_plan(s, s->size > 0 ? s->size : 1, s->dim, s->dtype, nq, k);
+    if (path) *path = sp.path == 2 && sp.quad ? 3 : sp.path;
+    if (tile_rows) *tile_rows = sp.levels.tile_rows;
+    if (num_levels) *num_levels = sp.levels.num_levels;
+    if (growth) *growth = sp.levels.growth;
+    if (strides)
+        for (int l = 0; l < kMaxLevels; l++) strides[l] = l < sp.levels.num_levels ? sp.levels.stride[l] : 0;
     return DAB_OK;
 }

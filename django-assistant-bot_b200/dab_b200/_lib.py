@@ -40,6 +40,8 @@ SIGNATURES = {
     "dab_merge_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "dab_search_noalloc": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p,
                                    c_void_p, c_void_p, c_void_p]),
+    "dab_store_describe_plan": (c_int, [c_void_p, c_int, c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int),
+                                        POINTER(c_int), POINTER(c_int)]),
     "dab_launch_count": (ctypes.c_uint64, []),
     "dab_store_set_profile": (c_int, [c_void_p, c_int]),
     "dab_store_get_profile": (c_int, [c_void_p, POINTER(ctypes.c_float), POINTER(c_int), POINTER(ctypes.c_float),

@@ -133,6 +133,16 @@ class ChunkStore:
     def set_spare_rounds(self, n: int) -> None:
         check(lib().dab_store_set_spare_rounds(self._h, int(n)))
 
+    def describe_plan(self, Q: int, k: int) -> dict:
+        """How a search of Q queries / top-k would run on the rows held now (path, tile, levels)."""
+        c = _lib.c_int
+        path, tile, levels, growth = c(), c(), c(), c()
+        strides = (c * 8)()
+        ref = _lib.ctypes.byref
+        check(lib().dab_store_describe_plan(self._h, int(Q), int(k), ref(path), ref(tile), ref(levels), ref(growth), strides))
+        return {"path": {1: "simt", 2: "tcgen05", 3: "tcgen05-cluster"}[path.value], "tile_rows": tile.value,
+                "num_levels": levels.value, "growth": growth.value, "strides": list(strides)[:levels.value]}
+
     def set_profile(self, on: bool) -> None:
         check(lib().dab_store_set_profile(self._h, 1 if on else 0))
 

@@ -188,8 +188,14 @@ DAB_API int dab_search_noalloc(const void *rows_dev, int rows_dtype, const float
  *                         cudaEvents on the caller's stream
  *   dab_store_get_profile synchronises the device, returns the summed event times since the
  *                         last call and clears them
+ *   dab_store_describe_plan  what a search of Q queries / top-k over the store's current rows would do:
+ *                         path (1 CUDA cores, 2 tcgen05, 3 tcgen05 4-CTA cluster kernel), rows per tile,
+ *                         number of sampling levels, growth factor and the tile stride of each level
+ *                         (strides[8], 0 past the last level).  Any output pointer may be NULL.
  */
 DAB_API uint64_t dab_launch_count(void);
+DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *path, int *tile_rows, int *num_levels, int *growth,
+                                    int *strides);
 DAB_API int dab_store_set_profile(dab_store *s, int on);
 DAB_API int dab_store_get_profile(dab_store *s, float *scan_ms, int *scan_launches, float *search_ms, int *searches);
 

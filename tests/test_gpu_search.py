@@ -107,20 +107,23 @@ def test_search_sorted_corpus():
 
 
 def test_search_clustered_corpus_overflows_and_recovers():
-    """29k near-copies of the query placed only in tiles that the sampled levels never visit
-    (tile = 64 rows here, levels sample every 1024th and every 32nd tile): the last level admits
-    far more than the 8192-slot candidate buffer.  The
-    unchecked call must report DAB_E_INCOMPLETE with poisoned outputs; the checked search must
-    retry on its own and return the exact answer."""
+    """~29k near-copies of the query placed only in tiles that the sampled levels never visit (the
+    plan is asked from the library): the last level admits far more than the 8192-slot candidate
+    buffer.  The unchecked call must report DAB_E_INCOMPLETE with poisoned outputs; the checked
+    search must retry on its own and return the exact answer."""
     from dab_b200 import _lib, ops
     g = torch.Generator().manual_seed(12)
     N, D, k = 300_000, 64, 10
     rows = torch.randn(N, D, generator=g)
     q = torch.randn(1, D, generator=g)
-    r = torch.arange(100_000, 130_000)
-    r = r[(r // 64) % 32 != 0]
-    rows[r] = q + 0.05 * torch.randn(r.numel(), D, generator=g)
     store = ops.ChunkStore(N, D, torch.float32, DEV)
+    store.append(rows.to(DEV))
+    plan = store.describe_plan(1, k)
+    assert plan["path"] == "simt" and plan["num_levels"] >= 2
+    r = torch.arange(100_000, 130_000)
+    r = r[(r // plan["tile_rows"]) % plan["strides"][-2] != 0]        # rows only the last level visits
+    rows[r] = q + 0.05 * torch.randn(r.numel(), D, generator=g)
+    store.reset()
     store.append(rows.to(DEV))
     s, i = store.search_async(q.to(DEV), k)
     rc = _lib.lib().dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
