@@ -215,6 +215,7 @@ def main():
     ap.add_argument("--workload", default=os.environ.get("DAB_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the corpus row count (debugging)")
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
+    ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="N>1: how local top-k lists are exchanged")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
     args = ap.parse_args()
@@ -261,8 +262,12 @@ def main():
     N, D, Q, k = w["rows"], w["dim"], w["Q"], w["k"]
     sdtype = torch.bfloat16 if w["dtype"] == "bf16" else torch.float32
     lo, hi = rank * N // world, (rank + 1) * N // world          # contiguous row shard, ids = global row index
-    store = ops.ChunkStore(hi - lo, D, sdtype, dev, id_base=lo)
+    from dab_b200 import sharded
+    sh = sharded.ShardedStore(N, D, sdtype, dev, exchange=args.exchange, max_q=max(Q, 1), max_k=max(k, 1))
+    assert (sh.lo, sh.hi) == (lo, hi)
+    store = sh.local
     store.set_path(args.path)
+    exchange = "none" if world == 1 else ("p2p" if sh.peer is not None else "nccl")
     sample_host = None
     r = lo
     while r < hi:
@@ -285,7 +290,13 @@ def main():
     gs = torch.empty(world, Q, k, dtype=torch.float32, device=dev) if world > 1 else None
     gi = torch.empty(world, Q, k, dtype=torch.int64, device=dev) if world > 1 else None
 
+    status_ptr = L.dab_store_status_dev(store._h)
+
     def step_device():
+        if sh.peer is not None:                         # one fused publish/wait/gather/merge kernel over NVLink
+            slot = sh.peer.next_slot(Q, k)
+            store.search_async(queries_dev, k, out=slot)
+            return sh.peer.merge(Q, k, status_ptr)
         s, i = store.search_async(queries_dev, k)
         if world > 1:
             dist.all_gather_into_tensor(gs, s)
@@ -295,11 +306,7 @@ def main():
 
     def step_e2e():
         qd = queries_host.to(dev, non_blocking=True)
-        s, i = store.search(qd, k)                      # checked search: includes its own status sync
-        if world > 1:
-            dist.all_gather_into_tensor(gs, s)
-            dist.all_gather_into_tensor(gi, i)
-            s, i = ops.merge_topk(gs, gi)
+        s, i = sh.search(qd, k)                         # the public, checked call (status sync, retries)
         out_host_s.copy_(s, non_blocking=True)
         out_host_i.copy_(i, non_blocking=True)
         torch.cuda.current_stream().synchronize()
@@ -378,7 +385,7 @@ def main():
                 warmup=args.warmup, ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="strong",
                 vs_baseline=None, dtype="bf16" if w["dtype"] == "bf16" and Q > 4 else "f32", data="synthetic",
                 config={"workload": args.workload, "desc": w["desc"], "rows": N, "rows_per_gpu": n_local, "dim": D,
-                        "store_dtype": w["dtype"], "Q": Q, "k": k, "path": args.path,
+                        "store_dtype": w["dtype"], "Q": Q, "k": k, "path": args.path, "exchange": exchange,
                         "arithmetic": ("bf16 x bf16 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
                                        if w["dtype"] == "bf16" and Q > 4 else "fp32 FMA dot products"),
                         "l2": "inputs larger than L2: every step streams the whole shard "

@@ -46,8 +46,8 @@ SearchScratch carve_scratch(void *base, int dim) {
 
 // Levels: level l scans the tiles t with t % stride[l] == 0 not scanned before, stride[l] =
 // growth^(L-1-l).  Level 0 is a strided sample small enough that every row may pass
-// (<= kCandCap/2 rows); each later level is (growth-1) times everything before it, so with a
-// threshold equal to the k-th best seen so far about k*(growth-1) <= kCandCap/2 rows pass.
+// (<= 3/4 kCandCap rows); each later level is (growth-1) times everything before it, so with a
+// threshold equal to the k-th best seen so far about k*(growth-1) <= 3/4 kCandCap rows pass.
 // The growth factor is the largest the candidate buffer tolerates (fewest levels = fewest kernel
 // boundaries), then shrunk to the smallest value that still gives that number of levels (fewest
 // admitted rows per level).
@@ -55,7 +55,8 @@ LevelPlan make_level_plan(int64_t n_rows, int tile_rows, int k_keep) {
     LevelPlan p = {};
     p.tile_rows = tile_rows;
     p.num_tiles = (n_rows + tile_rows - 1) / tile_rows;
-    const long long half_cap = kCandCap / 2;
+    // budget of rows a level may admit: 3/4 of the buffer (an occasional overflow is retried on the device)
+    const long long half_cap = (3 * kCandCap) / 4;
     long long gmax = half_cap / (k_keep > 0 ? k_keep : 1);
     if (gmax < 2) gmax = 2;
     if (gmax > 1024) gmax = 1024;

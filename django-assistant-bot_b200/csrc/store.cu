@@ -472,3 +472,9 @@ extern "C" DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *
         for (int l = 0; l < kMaxLevels; l++) strides[l] = l < sp.levels.num_levels ? sp.levels.stride[l] : 0;
     return DAB_OK;
 }
+
+// device address of {sticky_incomplete, sticky_inexact} of the store's last search (for dab_exchange_merge_topk)
+extern "C" DAB_API const int *dab_store_status_dev(dab_store *s) {
+    if (!s) return nullptr;
+    return &s->scratch.ctrl->sticky_incomplete;
+}

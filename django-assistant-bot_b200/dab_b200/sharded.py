@@ -3,13 +3,23 @@
 The reference keeps every embedding in a single PostgreSQL table
 (assistant/storage/models.py:19-58); here rows are sharded contiguously over the ranks,
 shard ``g`` holding rows ``[g*N/G, (g+1)*N/G)`` with ids = global row index.  A search runs the
-exact local top-k on every GPU (``ChunkStore.search``), all-gathers the ``(Q, k)`` score and id
-lists (``Q*k*12`` bytes per rank, NCCL over NVLink) and merges them with ``dab_merge_topk``:
-global top-k is a subset of the union of local top-k lists, so the result equals the
-single-table ``ORDER BY distance LIMIT n`` (assistant/rag/services/search_service.py:192-194).
+exact local top-k on every GPU (``ChunkStore``), exchanges the ``(Q, k)`` score and id lists
+(``Q*k*12`` bytes per rank) and merges them: global top-k is a subset of the union of local top-k
+lists, so the result equals the single-table ``ORDER BY distance LIMIT n``
+(assistant/rag/services/search_service.py:192-194).
+
+Two transports for the exchange:
+
+* ``"p2p"`` (default on NCCL/CUDA when torch symmetric memory can be set up): every rank's search
+  writes its lists straight into a peer-mapped staging block and ONE kernel
+  (``dab_exchange_merge_topk``) publishes, waits for the peers, pulls their lists over NVLink and
+  merges - no NCCL call on the data path; the ranks' search verdicts are OR-ed in the same kernel so
+  that every rank takes the same retry decision.
+* ``"nccl"``: ``all_gather_into_tensor`` of scores and ids, then ``dab_merge_topk``.
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Optional, Tuple
 
 import torch
@@ -49,10 +59,68 @@ def gather_topk(scores: torch.Tensor, ids: torch.Tensor, group=None) -> Tuple[to
     return gs.view((world,) + tuple(scores.shape)), gi.view((world,) + tuple(ids.shape))
 
 
+class PeerExchange:
+    """Peer-mapped staging block + the fused publish/wait/gather/merge kernel."""
+
+    def __init__(self, device: torch.device, group=None, max_q: int = 256, max_k: int = 256):
+        import torch.distributed._symmetric_memory as symm
+        from ._lib import lib
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.max_q, self.max_k = int(max_q), int(max_k)
+        self.device = device
+        nbytes = int(lib().dab_exchange_bytes(self.world, self.max_q, self.max_k))
+        self.buf = symm.empty(nbytes, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, self.group)
+        torch.cuda.synchronize(device)
+        self.hdl.barrier()                       # every rank's block is zeroed before anyone publishes
+        self.bases_dev = int(self.hdl.buffer_ptrs_dev)
+        self.epoch = 0
+        self.status_dev = torch.zeros(2, dtype=torch.int32, device=device)
+        self.status_host = torch.zeros(2, dtype=torch.int32).pin_memory()
+
+    def fits(self, Q: int, k: int) -> bool:
+        return Q <= self.max_q and k <= self.max_k and self.world * k <= 8192
+
+    def next_slot(self, Q: int, k: int):
+        """Tensors viewing the slot this rank's next search must write (scores [Q,k] f32, ids [Q,k] i64)."""
+        from ._lib import check, lib
+        self.epoch += 1
+        ps, pi = ctypes.c_void_p(), ctypes.c_void_p()
+        check(lib().dab_exchange_slot(self.buf.data_ptr(), self.world, self.max_q, self.max_k, self.epoch,
+                                      ctypes.byref(ps), ctypes.byref(pi)))
+        off_s, off_i = ps.value - self.buf.data_ptr(), pi.value - self.buf.data_ptr()
+        s = self.buf[off_s: off_s + Q * k * 4].view(torch.float32).view(Q, k)
+        i = self.buf[off_i: off_i + Q * k * 8].view(torch.int64).view(Q, k)
+        return s, i
+
+    def merge(self, Q: int, k: int, local_status_ptr: Optional[int]):
+        """Launch the exchange kernel for the slot handed out last; returns merged (scores, ids) and
+        leaves the OR-ed verdict in ``status_dev``."""
+        from ._lib import check, lib
+        out_s = torch.empty((Q, k), dtype=torch.float32, device=self.device)
+        out_i = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib().dab_exchange_merge_topk(self.bases_dev, self.rank, self.world, self.max_q, self.max_k, Q, k,
+                                                self.epoch, local_status_ptr, out_s.data_ptr(), out_i.data_ptr(),
+                                                self.status_dev.data_ptr(),
+                                                torch.cuda.current_stream(self.device).cuda_stream))
+        return out_s, out_i
+
+    def verdict(self) -> Tuple[bool, bool]:
+        """(incomplete, inexact) of the last exchange, identical on every rank.  Synchronises."""
+        self.status_host.copy_(self.status_dev, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return bool(self.status_host[0]), bool(self.status_host[1])
+
+
 class ShardedStore:
     """This rank's shard of a corpus of ``total_rows`` rows + the merged search."""
 
-    def __init__(self, total_rows: int, dim: int, dtype: torch.dtype = torch.bfloat16, device=None, group=None):
+    def __init__(self, total_rows: int, dim: int, dtype: torch.dtype = torch.bfloat16, device=None, group=None,
+                 exchange: str = "auto", max_q: int = 256, max_k: int = 256):
         from . import ops
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -60,17 +128,57 @@ class ShardedStore:
         self.total_rows = int(total_rows)
         self.lo, self.hi = shard_bounds(self.total_rows, self.world, self.rank)
         self.local = ops.ChunkStore(max(1, self.hi - self.lo), dim, dtype, device, id_base=self.lo)
+        self.peer: Optional[PeerExchange] = None
+        if exchange not in ("auto", "p2p", "nccl"):
+            raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+        if self.world > 1 and exchange in ("auto", "p2p"):
+            try:
+                self.peer = PeerExchange(self.local.device, group, max_q, max_k)
+            except Exception:
+                if exchange == "p2p":
+                    raise
+                self.peer = None                 # symmetric memory unavailable: NCCL all-gather instead
 
     def append_local(self, rows: torch.Tensor) -> None:
         """Rows of THIS shard, in global row order."""
         self.local.append(rows)
 
+    def _search_p2p(self, queries: torch.Tensor, k: int, allow_bitmap):
+        from ._lib import lib
+        Q = queries.shape[0] if queries.dim() == 2 else 1
+        spare, forced_simt = 0, False
+        try:
+            while True:
+                slot = self.peer.next_slot(Q, k)
+                self.local.search_async(queries, k, allow_bitmap, out=slot)
+                s, i = self.peer.merge(Q, k, lib().dab_store_status_dev(self.local._h))
+                incomplete, inexact = self.peer.verdict()          # same answer on every rank
+                if inexact and not forced_simt:
+                    lib().dab_store_set_path(self.local._h, 1)
+                    forced_simt = True
+                    continue
+                if not incomplete:
+                    return s, i
+                spare = 4 if spare == 0 else spare * 2
+                if spare > 64:
+                    from ._lib import DabError
+                    raise DabError(5, "sharded search did not complete within 64 spare rounds")
+                self.local.set_spare_rounds(spare)
+        finally:
+            if spare:
+                self.local.set_spare_rounds(0)
+            if forced_simt:
+                lib().dab_store_set_path(self.local._h, self.local._path)
+
     def search(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None):
         """Replicated queries in, identical merged ``(scores [Q,k], ids [Q,k])`` out on every rank."""
         from . import ops
-        s, i = self.local.search(queries, k, allow_bitmap)
         if self.world == 1:
-            return s, i
+            return self.local.search(queries, k, allow_bitmap)
+        Q = queries.shape[0] if queries.dim() == 2 else 1
+        if self.peer is not None and self.peer.fits(Q, k):
+            return self._search_p2p(queries, k, allow_bitmap)
+        s, i = self.local.search(queries, k, allow_bitmap)
         gs, gi = gather_topk(s, i, self.group)
         return ops.merge_topk(gs, gi)
 

@@ -149,6 +149,28 @@ DAB_API int dab_merge_topk(const float *gathered_scores_dev, const int64_t *gath
                    float *out_scores_dev, int64_t *out_ids_dev, void *stream);
 
 /*
+ * The exchange step of the sharded search as ONE kernel over NVLink peer memory (no NCCL call):
+ * publish "my local top-k is ready" to every peer, wait for all peers, pull their lists with
+ * peer loads and merge - all ranks launch it once per search (SPMD).  New in the build, like
+ * dab_merge_topk.  Every rank owns one staging block of dab_exchange_bytes(R, max_q, max_k) bytes,
+ * zero-initialised, mapped into every peer (e.g. torch symmetric memory); peer_bases_dev is a
+ * DEVICE array of the R mapped base addresses, in rank order.
+ *   dab_exchange_slot     where search number `epoch` (1, 2, 3, ...) must write this rank's lists:
+ *                         pass these as out_scores/out_ids of dab_store_search
+ *   dab_store_status_dev  device address of the store's {incomplete, inexact} verdict (2 ints)
+ *   dab_exchange_merge_topk  out_scores/out_ids [Q,k] merged (score desc, id asc); out_status (2 ints,
+ *                         device, may be NULL) = OR over all ranks of the verdicts, so that every rank
+ *                         takes the same retry decision.  R*k <= 8192.  A peer that never
+ *                         publishes makes the kernel trap after a bounded spin instead of hanging.
+ */
+DAB_API int64_t dab_exchange_bytes(int R, int max_q, int max_k);
+DAB_API int dab_exchange_slot(void *base, int R, int max_q, int max_k, uint32_t epoch, float **scores, int64_t **ids);
+DAB_API const int *dab_store_status_dev(dab_store *s);
+DAB_API int dab_exchange_merge_topk(void *const *peer_bases_dev, int rank, int R, int max_q, int max_k, int Q, int k,
+                                    uint32_t epoch, const int *local_status_dev_or_null, float *out_scores_dev,
+                                    int64_t *out_ids_dev, int *out_status_dev_or_null, void *stream);
+
+/*
  * Exact cosine top-k over rows the CALLER owns, without allocating anything.
  * No counterpart in the reference (there the rows live in PostgreSQL and the executor
  * allocates as it pleases); it exists for hosts of this library that cannot call cudaMalloc:

@@ -21,12 +21,21 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
 N, D, Q, k = 200_000, 768, 16, 50
 g = torch.Generator().manual_seed(1)
 rows = torch.randn(N, D, generator=g); queries = torch.randn(Q, D, generator=g)
-st = sharded.ShardedStore(N, D, torch.bfloat16, torch.device("cuda", rank))
-st.append_local(rows[st.lo:st.hi].cuda())
-s, i = st.search(queries.cuda(), k)
 S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), queries.numpy())
-for q in range(Q):
-    search_ref.check_topk_parity(S[q], i[q].cpu().numpy(), s[q].cpu().numpy(), k)
+results = {}
+for mode in ("p2p", "nccl"):
+    st = sharded.ShardedStore(N, D, torch.bfloat16, torch.device("cuda", rank), exchange=mode)
+    assert (st.peer is not None) == (mode == "p2p")
+    st.append_local(rows[st.lo:st.hi].cuda())
+    for rep in range(3):                                  # several epochs: the staging slots alternate
+        s, i = st.search(queries.cuda(), k)
+        for q in range(Q):
+            search_ref.check_topk_parity(S[q], i[q].cpu().numpy(), s[q].cpu().numpy(), k)
+    s1, i1 = st.search(queries[:1].cuda(), 7)             # another shape through the same staging block
+    search_ref.check_topk_parity(S[0], i1[0].cpu().numpy(), s1[0].cpu().numpy(), 7)
+    results[mode] = (s.cpu(), i.cpu())
+    st.close()
+assert torch.equal(results["p2p"][1], results["nccl"][1]) and torch.equal(results["p2p"][0], results["nccl"][0])
 dist.barrier(); dist.destroy_process_group(); print("rank", rank, "ok")
 '''
 
