@@ -46,43 +46,26 @@ SearchScratch carve_scratch(void *base, int dim) {
 
 // Levels: level l scans the tiles t with t % stride[l] == 0 not scanned before, stride[l] =
 // growth^(L-1-l).  Level 0 is a strided sample small enough that every row may pass
-// (<= 3/4 kCandCap rows); each later level is (growth-1) times everything before it, so with a
-// threshold equal to the k-th best seen so far about k*(growth-1) <= 3/4 kCandCap rows pass.
-// The growth factor is the largest the candidate buffer tolerates (fewest levels = fewest kernel
-// boundaries), then shrunk to the smallest value that still gives that number of levels (fewest
-// admitted rows per level).
+// (<= kCandCap/2 rows); each later level is (growth-1) times everything before it, so with a
+// threshold equal to the k-th best seen so far about k*(growth-1) <= kCandCap/2 rows pass.
+// Growth is capped at 32: measured on B200, fewer but fatter levels (growth 163-245 for k = 10,
+// 13 instead of 8 for the tensor path) were SLOWER - every admitted row costs an atomic append in
+// the scan and the compaction sort grows with the admitted count - than one more kernel boundary.
 LevelPlan make_level_plan(int64_t n_rows, int tile_rows, int k_keep) {
     LevelPlan p = {};
     p.tile_rows = tile_rows;
     p.num_tiles = (n_rows + tile_rows - 1) / tile_rows;
-    // budget of rows a level may admit: 3/4 of the buffer (an occasional overflow is retried on the device)
-    const long long half_cap = (3 * kCandCap) / 4;
-    long long gmax = half_cap / (k_keep > 0 ? k_keep : 1);
-    if (gmax < 2) gmax = 2;
-    if (gmax > 1024) gmax = 1024;
-    auto levels_for = [&](long long g) {
-        int L = 1;
-        long long s0 = 1;
-        while (L < kMaxLevels && ((p.num_tiles + s0 - 1) / s0) * tile_rows > half_cap) {
-            s0 *= g;
-            L++;
-        }
-        return L;
-    };
-    const int L = levels_for(gmax);
-    long long g = gmax;
-    if (L > 1) {  // smallest growth with the same level count (binary search; levels_for is monotone in g)
-        long long lo = 2, hi = gmax;
-        while (lo < hi) {
-            const long long mid = (lo + hi) / 2;
-            if (levels_for(mid) <= L) hi = mid; else lo = mid + 1;
-        }
-        g = lo;
+    int g = 32;
+    while (g > 2 && (long long)g * k_keep > kCandCap / 2) g >>= 1;
+    p.growth = g;
+    int L = 1;
+    long long s0 = 1;
+    while (L < kMaxLevels && ((p.num_tiles + s0 - 1) / s0) * tile_rows > kCandCap / 2) {
+        s0 *= g;
+        L++;
     }
-    p.growth = (int)g;
     p.num_levels = L;
-    long long s = 1;
-    for (int l = 1; l < L; l++) s *= g;
+    long long s = s0;
     for (int l = 0; l < L; l++) {
         p.stride[l] = (int)s;
         const long long m = (p.num_tiles + s - 1) / s;
