@@ -33,7 +33,6 @@ namespace {
 
 using namespace umma;
 constexpr int kThreads = 256;
-constexpr int kCluster = 4;
 constexpr int kMaxStages = 8;
 constexpr int kMinStages = 3;
 constexpr int kPendCap = 512;       // staged candidates per accumulator stage per CTA
@@ -66,6 +65,13 @@ __device__ __forceinline__ void tma_load_2d_mc2(void *smem_dst, const CUtensorMa
         ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "h"(mask), "r"(c0), "r"(c1)
         : "memory");
 }
+// A-tile load into THIS CTA only; complete_tx goes to the pair leader's mbarrier
+__device__ __forceinline__ void tma_load_2d_2cta(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_alloc2(uint32_t *smem_out, uint32_t cols) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)), "r"(cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
@@ -91,14 +97,15 @@ __device__ __forceinline__ void umma_commit_mc2(uint64_t *bar, uint16_t mask) {
 __global__ void __launch_bounds__(kThreads, 1)
 scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
                       const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pair, int stages,
-                      int tmem_cols, const __grid_constant__ LevelPlan plan) {
+                      int tmem_cols, int num_pairs, const __grid_constant__ LevelPlan plan) {
     extern __shared__ unsigned char smem_raw[];
     const int lvl = sc.ctrl->cur_level;
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];  // super-tiles of 256 rows
-    const int cluster_id = blockIdx.x / kCluster;
-    const int num_clusters = gridDim.x / kCluster;
-    if ((long long)cluster_id >= ntiles) return;       // same decision in all 4 CTAs of the cluster
+    const int cluster_size = 2 * num_pairs;             // 4 = two pairs sharing one tile stream; 2 = one pair
+    const int cluster_id = blockIdx.x / cluster_size;
+    const int num_clusters = gridDim.x / cluster_size;
+    if ((long long)cluster_id >= ntiles) return;       // same decision in every CTA of the cluster
 
     const uint32_t rank = cluster_ctarank();
     const int pair = (int)(rank >> 1), half = (int)(rank & 1);
@@ -130,7 +137,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     if (tid == 0) {
         for (int s = 0; s < stages; s++) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], 2);
+            mbar_init(&empty[s], (uint32_t)num_pairs);
         }
         mbar_init(b_full, 1);
         mbar_init(b_pair, 2);
@@ -165,7 +172,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             if (rank < 2) {
                 // A tiles for the whole cluster: my 128-row half of every super-tile, multicast to my
                 // twin in the other pair
-                const uint16_t mask = (uint16_t)((1u << rank) | (1u << (rank + 2)));
+                const uint16_t mask = (uint16_t)((1u << rank) | (num_pairs == 2 ? (1u << (rank + 2)) : 0u));
                 int s = 0;
                 uint32_t ph = 0;
                 for (long long it = 0; it < my_tiles; it++) {
@@ -173,7 +180,10 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                     const int row0 = (int)(t * kSuperRows) + half * kTileRows;
                     for (int kb = 0; kb < num_kb; kb++) {
                         mbar_wait_bounded(&empty[s], ph ^ 1u);
-                        tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s], mask);
+                        if (num_pairs == 2)
+                            tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s], mask);
+                        else
+                            tma_load_2d_2cta(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s]);
                         if (++s == stages) { s = 0; ph ^= 1u; }
                     }
                 }
@@ -273,9 +283,9 @@ struct QuadPlan {
     size_t smem;
 };
 
-// n_pair = queries per CTA pair (multiple of 32: each CTA's B quarter must be a multiple of 16 rows)
-bool plan_quad(int dim, int nq, QuadPlan *out) {
-    int n_pair = ((nq + 1) / 2 + 31) / 32 * 32;
+// n_pair = queries per CTA pair (multiple of 32: each CTA's share of B must be a multiple of 16 rows)
+bool plan_quad(int dim, int nq, int num_pairs, QuadPlan *out) {
+    int n_pair = ((nq + num_pairs - 1) / num_pairs + 31) / 32 * 32;
     if (n_pair < 32) n_pair = 32;
     if (n_pair > 128) return false;
     const size_t b_bytes = (size_t)(n_pair / 2) * dim * 2;
@@ -299,13 +309,24 @@ int quad_tile_rows() { return kSuperRows; }
 
 bool quad_supported(int dim, int dtype, int nq) {
     QuadPlan p;
-    return dtype == DAB_BF16 && dim % kBlockK == 0 && nq >= 1 && nq <= DAB_MAX_QUERY_BATCH && plan_quad(dim, nq, &p);
+    return dtype == DAB_BF16 && dim % kBlockK == 0 && nq >= 1 && nq <= DAB_MAX_QUERY_BATCH && plan_quad(dim, nq, 2, &p);
+}
+
+// the most queries ONE pair (cluster of 2, no multicast) can score per corpus pass
+int pair_queries_per_pass(int dim) {
+    int best = 0;
+    QuadPlan p;
+    for (int n = 32; n <= 256; n += 32)
+        if (plan_quad(dim, n, 1, &p)) best = n;
+    return best;
 }
 
 int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
-                          const LevelPlan &plan, int num_sms, cudaStream_t st) {
+                          const LevelPlan &plan, int num_sms, cudaStream_t st, int num_pairs) {
     QuadPlan qp;
-    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK || !plan_quad(sv.dim, nq, &qp))
+    if (num_pairs != 1 && num_pairs != 2) return fail(DAB_E_INVALID, "scan_umma_quad: 1 or 2 pairs per cluster");
+    const int kCluster = 2 * num_pairs;
+    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK || !plan_quad(sv.dim, nq, num_pairs, &qp))
         return fail(DAB_E_INVALID, "scan_umma_quad: needs a bf16 store, dim % 64 == 0 and <= 256 queries that fit shared memory");
     if (plan.tile_rows != kSuperRows) return fail(DAB_E_INVALID, "scan_umma_quad: level plan built for another tile size");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
@@ -335,11 +356,11 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     const long long clusters = max_tiles < max_clusters ? max_tiles : max_clusters;
     static const bool debug = getenv("DAB_DEBUG") != nullptr;
     if (debug)
-        fprintf(stderr, "[dab] quad: nq=%d n_pair=%d stages=%d tmem_cols=%d smem=%zu max_clusters=%d clusters=%lld levels=%d\n", nq,
+        fprintf(stderr, "[dab] quad: pairs=%d nq=%d n_pair=%d stages=%d tmem_cols=%d smem=%zu max_clusters=%d clusters=%lld levels=%d\n", num_pairs, nq,
                 qp.n_pair, qp.stages, qp.tmem_cols, qp.smem, max_clusters, clusters, plan.num_levels);
     cfg.gridDim = dim3((unsigned)(clusters * kCluster), 1, 1);
     DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, scan_umma_quad_kernel, tmap_rows, tmap_q, sv, allow, sc, q0, nq, qp.n_pair, qp.stages,
-                                   qp.tmem_cols, plan));
+                                   qp.tmem_cols, num_pairs, plan));
     count_launch();
     return DAB_OK;
 }

@@ -333,8 +333,14 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
             {
                 // one launch scores all nq queries
                 ScanTimer tm(s->prof, st);
-                if (int rc = sp.quad ? launch_scan_umma_quad(sv, allow, sc, 0, nq, plan, s->num_sms, st)
-                                     : launch_scan_umma(sv, allow, sc, 0, nq, plan, s->num_sms, st))
+                static const bool pair_mode = getenv("DAB_WIDE_PAIRS") != nullptr;  // tuning aid
+                if (sp.quad && pair_mode) {
+                    const int per = pair_queries_per_pass(sv.dim);
+                    for (int q0 = 0; q0 < nq; q0 += per)
+                        if (int rc = launch_scan_umma_quad(sv, allow, sc, q0, nq - q0 < per ? nq - q0 : per, plan, s->num_sms, st, 1))
+                            return rc;
+                } else if (int rc = sp.quad ? launch_scan_umma_quad(sv, allow, sc, 0, nq, plan, s->num_sms, st)
+                                            : launch_scan_umma(sv, allow, sc, 0, nq, plan, s->num_sms, st))
                     return rc;
                 tm.stop();
             }

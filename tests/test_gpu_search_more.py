@@ -1,0 +1,118 @@
+"""More parity cases for the device store: explicit ids, query chunks beyond 256, filters on the
+tensor-core paths, the largest k, reset/reuse, 1-D queries."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import search_ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _oracle_check(stored, queries, ids, scores, k, allow=None, row_of_id=None):
+    S = search_ref.exact_scores(stored, queries)
+    for qi in range(queries.shape[0]):
+        got = ids[qi] if row_of_id is None else np.array([row_of_id.get(int(x), -1) for x in ids[qi]])
+        search_ref.check_topk_parity(S[qi], got, scores[qi], k, allow=allow)
+
+
+@pytest.mark.parametrize("dtype,path", [(torch.float32, "simt"), (torch.bfloat16, "tcgen05")])
+def test_explicit_ids_are_returned(dtype, path):
+    """Rows appended with Django pks: results carry the pks; ties still break by row order."""
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(1)
+    N, D, Q, k = 30_000, 768, 6, 25
+    rows = torch.randn(N, D, generator=g)
+    pks = (torch.arange(N) * 3 + 1000)                       # ascending with insertion order
+    rows[20_000] = rows[17]
+    queries = torch.randn(Q, D, generator=g)
+    queries[0] = rows[17]
+    store = ops.ChunkStore(N, D, dtype, DEV)
+    store.set_path(path)
+    store.append(rows[:10_000].to(DEV), pks[:10_000].to(DEV))
+    store.append(rows[10_000:].to(DEV), pks[10_000:].to(DEV))
+    scores, ids = store.search(queries.to(DEV), k)
+    ids, scores = ids.cpu().numpy(), scores.cpu().numpy()
+    row_of = {int(p): i for i, p in enumerate(pks.tolist())}
+    _oracle_check(rows.to(dtype).float().numpy(), queries.numpy(), ids, scores, k, row_of_id=row_of)
+    assert ids[0, 0] == 1000 + 3 * 17 and ids[0, 1] == 1000 + 3 * 20_000
+    from dab_b200 import DabError
+    with pytest.raises(DabError, match="explicit and implicit ids"):
+        store.append(rows[:5].to(DEV))
+    store.close()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_more_than_256_queries_are_chunked(dtype):
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(2)
+    N, D, Q, k = 20_000, 128, 300, 7
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    store = ops.ChunkStore(N, D, dtype, DEV, id_base=5_000_000_000)          # ids beyond 32 bits
+    store.append(rows.to(DEV))
+    scores, ids = store.search(queries.to(DEV), k)
+    _oracle_check(rows.to(dtype).float().numpy(), queries.numpy(), ids.cpu().numpy() - 5_000_000_000, scores.cpu().numpy(), k)
+    store.close()
+
+
+@pytest.mark.parametrize("Q", [16, 200])
+def test_row_filter_on_tensor_core_paths(Q):
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(3 + Q)
+    N, D, k = 60_000, 768, 30
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    allow = torch.rand(N, generator=g) < 0.2
+    store = ops.ChunkStore(N, D, torch.bfloat16, DEV)
+    store.set_path("tcgen05")
+    store.append(rows.to(DEV))
+    scores, ids = store.search(queries.to(DEV), k, ops.pack_allow_bitmap(allow.to(DEV)))
+    _oracle_check(rows.to(torch.bfloat16).float().numpy(), queries.numpy(), ids.cpu().numpy(), scores.cpu().numpy(), k,
+                  allow=allow.numpy())
+    store.close()
+
+
+@pytest.mark.parametrize("dtype,path", [(torch.float32, "simt"), (torch.bfloat16, "tcgen05")])
+def test_largest_k_and_reset_reuse(dtype, path):
+    from dab_b200 import _lib, ops
+    g = torch.Generator().manual_seed(4)
+    N, D = 50_000, 64
+    rows = torch.randn(N, D, generator=g)
+    q = torch.randn(2, D, generator=g)
+    store = ops.ChunkStore(N, D, dtype, DEV)
+    store.set_path(path)
+    store.append(rows.to(DEV))
+    k = _lib.DAB_MAX_K
+    scores, ids = store.search(q.to(DEV), k)
+    _oracle_check(rows.to(dtype).float().numpy(), q.numpy(), ids.cpu().numpy(), scores.cpu().numpy(), k)
+    # reset and refill with other rows: nothing of the old contents may leak into the answers
+    store.reset()
+    assert len(store) == 0
+    rows2 = torch.randn(1000, D, generator=g)
+    store.append(rows2.to(DEV))
+    s1, i1 = store.search(q[0].to(DEV), 5)                                    # 1-D query
+    assert s1.shape == (1, 5)
+    _oracle_check(rows2.to(dtype).float().numpy(), q[:1].numpy(), i1.cpu().numpy(), s1.cpu().numpy(), 5)
+    store.close()
+
+
+def test_randomised_shapes_against_oracle():
+    """A seeded sweep over odd shapes (dims that are not multiples of 64, k near N, tiny N)."""
+    from dab_b200 import ops
+    rng = np.random.default_rng(2026)
+    for trial in range(12):
+        dtype = torch.bfloat16 if trial % 2 else torch.float32
+        D = int(rng.choice([8, 24, 200, 392, 520, 1000] if dtype == torch.bfloat16 else [4, 12, 100, 388, 516, 1004]))
+        N = int(rng.integers(1, 6000))
+        Q = int(rng.integers(1, 40))
+        k = int(rng.integers(1, min(N, 300) + 1))
+        g = torch.Generator().manual_seed(trial)
+        rows = torch.randn(N, D, generator=g)
+        queries = torch.randn(Q, D, generator=g)
+        store = ops.ChunkStore(N, D, dtype, DEV)
+        store.append(rows.to(DEV))
+        scores, ids = store.search(queries.to(DEV), k)
+        _oracle_check(rows.to(dtype).float().numpy(), queries.numpy(), ids.cpu().numpy(), scores.cpu().numpy(), k)
+        store.close()
