@@ -38,6 +38,8 @@ SIGNATURES = {
     "dab_store_set_spare_rounds": (c_int, [c_void_p, c_int]),
     "dab_store_set_path": (c_int, [c_void_p, c_int]),
     "dab_merge_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "dab_doc_aggregate": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                  c_void_p]),
     "dab_exchange_bytes": (c_int64, [c_int, c_int, c_int]),
     "dab_exchange_slot": (c_int, [c_void_p, c_int, c_int, c_int, ctypes.c_uint32, POINTER(c_void_p), POINTER(c_void_p)]),
     "dab_store_status_dev": (c_void_p, [c_void_p]),

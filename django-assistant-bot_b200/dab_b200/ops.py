@@ -232,6 +232,27 @@ class ChunkStore:
                     lib().dab_store_set_path(self._h, self._path)
 
 
+def doc_aggregate(scores: torch.Tensor, rows: torch.Tensor, doc_of_row: torch.Tensor, max_scores_n: int, top_n: int):
+    """Device form of the grouping in ``embedding_search`` (assistant/rag/services/search_service.py:133-150).
+    ``scores``/``rows`` [Q,n] as returned by ``ChunkStore.search`` on a store with implicit ids;
+    ``doc_of_row`` [N] int64.  Returns (doc_ids [Q,top_n] int64 with -1 padding, doc_scores [Q,top_n] fp32)."""
+    for t, name in ((scores, "scores"), (rows, "rows"), (doc_of_row, "doc_of_row")):
+        _need_cuda(t, name)
+    if scores.dim() != 2 or scores.shape != rows.shape:
+        raise DabError(_lib.DAB_E_INVALID, "scores and rows must both be [Q,n]")
+    scores = scores.to(torch.float32).contiguous()
+    rows = rows.to(torch.int64).contiguous()
+    doc_of_row = doc_of_row.to(torch.int64).contiguous()
+    Q, n = scores.shape
+    dev = scores.device
+    out_docs = torch.empty((Q, top_n), dtype=torch.int64, device=dev)
+    out_scores = torch.empty((Q, top_n), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().dab_doc_aggregate(scores.data_ptr(), rows.data_ptr(), doc_of_row.data_ptr(), doc_of_row.numel(), Q, n,
+                                      int(max_scores_n), int(top_n), out_docs.data_ptr(), out_scores.data_ptr(), _stream(dev)))
+    return out_docs, out_scores
+
+
 def merge_topk(gathered_scores: torch.Tensor, gathered_ids: torch.Tensor):
     """k-way merge of per-shard results: [R,Q,k] -> [Q,k] under (score desc, id asc)."""
     _need_cuda(gathered_scores, "gathered_scores")

@@ -85,6 +85,7 @@ class DeviceTable:
         self._meta: Dict[str, List[Any]] = {}
         self._cols: Dict[str, np.ndarray] = {}
         self._row_of_pk: Dict[int, int] = {}
+        self._doc_dev: Optional[torch.Tensor] = None     # device copy of the document_id column (lazy)
         self.documents: Dict[int, Any] = {}
 
     def __len__(self):
@@ -153,6 +154,23 @@ class DeviceTable:
         scores, ids = self.store.search(q.to(self.device), k, bitmap)
         scores, ids = scores.cpu().numpy().astype(np.float64), ids.cpu().numpy()
         return 1.0 - scores, ids
+
+    def search_documents(self, query_embedding, n: int, max_scores_n: int, top_n: int,
+                         bitmap: Optional[torch.Tensor] = None) -> List[Tuple[int, float]]:
+        """Device form of search_service.py:129-150: top-n rows, grouped per document, best ``top_n``
+        ``(document_id, score)`` pairs."""
+        q = torch.as_tensor(np.asarray(query_embedding, dtype=np.float32))
+        if q.shape[-1] != self.dim:
+            raise DabError(3, f"different vector dimensions {q.shape[-1]} and {self.dim}")
+        if len(self) == 0:
+            return []
+        if self._doc_dev is None or self._doc_dev.numel() != len(self):
+            self._doc_dev = torch.as_tensor(np.asarray(self._doc, dtype=np.int64)).to(self.device)
+        k = min(int(n), ops._lib.DAB_MAX_K)
+        scores, rows = self.store.search(q.to(self.device), k, bitmap)
+        docs, dscores = ops.doc_aggregate(scores, rows, self._doc_dev, max_scores_n, top_n)
+        docs, dscores = docs[0].cpu().tolist(), dscores[0].cpu().tolist()
+        return [(int(d), float(s)) for d, s in zip(docs, dscores) if d >= 0]
 
     def hits(self, dist_row: np.ndarray, rows_row: np.ndarray) -> List[ChunkRow]:
         out = []
@@ -301,11 +319,15 @@ async def embedding_search(query: str, qs, max_scores_n: int = 10, top_n: int = 
     rows (:129-131), aggregate per document."""
     logger.info(f'Embedding search for query: {query}')
     query_embedding = await get_embedding(query)
-    top_objects = await _objects_embedding_search(query_embedding, qs, n=max_scores_n * top_n * 10)
-    scored = aggregate_documents(top_objects, max_scores_n, top_n)
+    n = max_scores_n * top_n * 10
     if isinstance(qs, ChunkQuerySet):
+        # search + grouping both on the device: only <= top_n (doc id, score) pairs come back to the host
+        scored = await asyncio.to_thread(qs.table.search_documents, query_embedding, n, max_scores_n, top_n,
+                                         qs.allow_bitmap())
         lookup = qs.table.documents
         return [(lookup.get(doc_id, doc_id), score) for doc_id, score in scored]
+    top_objects = await _objects_embedding_search(query_embedding, qs, n=n)
+    scored = aggregate_documents(top_objects, max_scores_n, top_n)
     doc_model = qs.model._meta.get_field('document').related_model
     found = {d.id: d for d in await asyncio.to_thread(
         lambda: list(doc_model.objects.filter(id__in=[d for d, _ in scored])))}

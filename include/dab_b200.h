@@ -149,6 +149,21 @@ DAB_API int dab_merge_topk(const float *gathered_scores_dev, const int64_t *gath
                    float *out_scores_dev, int64_t *out_ids_dev, void *stream);
 
 /*
+ * Document-level aggregation of the hits of a search, on the device.
+ * Replaces: the grouping loop of `embedding_search`,
+ *           assistant/rag/services/search_service.py:133-150 - hits grouped by document_id in rank
+ *           order, documents with fewer than max_scores_n hits dropped, score
+ *           1 - sum(first max_scores_n distances)/max_scores_n, best top_n (ties: first appearance).
+ *   scores_dev/rows_dev  [Q,n] output of dab_store_search on a store with implicit ids (id = row)
+ *   doc_of_row_dev       [n_rows] int64 document id of every store row
+ *   out_doc_ids_dev      [Q,top_n] int64 (-1 = fewer documents qualified), out_doc_scores_dev [Q,top_n] fp32
+ * n <= 4096.
+ */
+DAB_API int dab_doc_aggregate(const float *scores_dev, const int64_t *rows_dev, const int64_t *doc_of_row_dev,
+                              int64_t n_rows, int Q, int n, int max_scores_n, int top_n, int64_t *out_doc_ids_dev,
+                              float *out_doc_scores_dev, void *stream);
+
+/*
  * The exchange step of the sharded search as ONE kernel over NVLink peer memory (no NCCL call):
  * publish "my local top-k is ready" to every peer, wait for all peers, pull their lists with
  * peer loads and merge - all ranks launch it once per search (SPMD).  New in the build, like

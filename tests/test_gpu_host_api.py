@@ -169,3 +169,26 @@ def test_endpoint_with_b200_embedder():
         np.testing.assert_allclose(np.linalg.norm(e, axis=1), 1.0, rtol=1e-5)
         r = c.post("/embeddings/", json={"model": "minilm", "texts": ["not-in-the-stub-vocabulary"]})
         assert r.status_code == 500        # tokenizer KeyError surfaces as HTTP 500 with str(e)
+
+
+@pytest.mark.parametrize("n,max_scores_n,top_n", [(250, 5, 5), (40, 1, 3), (1000, 10, 10), (64, 40, 2), (7, 2, 4)])
+def test_doc_aggregate_kernel_matches_oracle(n, max_scores_n, top_n):
+    """dab_doc_aggregate == oracle restatement of search_service.py:133-150 on random hit lists."""
+    from dab_b200 import ops
+    rng = np.random.default_rng(n * 31 + max_scores_n)
+    Q, N = 6, 5000
+    doc_of_row = rng.integers(0, max(3, n // 8), size=N).astype(np.int64)
+    scores = np.sort(rng.random((Q, n)).astype(np.float32), axis=1)[:, ::-1].copy()
+    rows = np.stack([rng.permutation(N)[:n] for _ in range(Q)]).astype(np.int64)
+    rows[1, n // 2:] = -1                                   # a query with fewer hits than n
+    docs, dsc = ops.doc_aggregate(torch.from_numpy(scores).to(DEV), torch.from_numpy(rows).to(DEV),
+                                  torch.from_numpy(doc_of_row).to(DEV), max_scores_n, top_n)
+    docs, dsc = docs.cpu().numpy(), dsc.cpu().numpy()
+    for q in range(Q):
+        valid = rows[q] >= 0
+        want = search_ref.doc_level_scores(doc_of_row[rows[q][valid]], 1.0 - scores[q][valid].astype(np.float64),
+                                           max_scores_n, top_n)
+        got = [(int(d), float(s)) for d, s in zip(docs[q], dsc[q]) if d >= 0]
+        assert [d for d, _ in got] == [d for d, _ in want], (q, got, want)
+        np.testing.assert_allclose([s for _, s in got], [s for _, s in want], atol=2e-6)
+        assert (docs[q][len(want):] == -1).all()

@@ -28,7 +28,7 @@ def test_explicit_ids_are_returned(dtype, path):
     rows[20_000] = rows[17]
     queries = torch.randn(Q, D, generator=g)
     queries[0] = rows[17]
-    store = ops.ChunkStore(N, D, dtype, DEV)
+    store = ops.ChunkStore(N + 8, D, dtype, DEV)
     store.set_path(path)
     store.append(rows[:10_000].to(DEV), pks[:10_000].to(DEV))
     store.append(rows[10_000:].to(DEV), pks[10_000:].to(DEV))
