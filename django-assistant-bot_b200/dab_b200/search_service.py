@@ -299,6 +299,37 @@ async def embedding_search_sentences(query_embedding: List[float], qs, n: int = 
     return await _objects_embedding_search(query_embedding, qs, n)
 
 
+def _search_many_sync(query_embeddings, qs, n: int, field: str):
+    table, bitmap, model = _table_and_bitmap(qs, field)
+    dist, rows = table.search_rows(query_embeddings, n, bitmap)
+    per_query = [table.hits(dist[i], rows[i]) for i in range(dist.shape[0])]
+    if model is None:
+        return per_query
+    objs = model.objects.in_bulk(sorted({h.pk for hits in per_query for h in hits}))
+    out = []
+    for hits in per_query:
+        cur = []
+        for h in hits:
+            o = objs.get(h.pk)
+            if o is not None:
+                import copy
+                o = copy.copy(o)          # the same row may be a hit of several queries with different distances
+                o.distance = h.distance
+                cur.append(o)
+        out.append(cur)
+    return out
+
+
+async def embedding_search_many(query_embeddings: List[List[float]], qs, n: int = 10, field: str = 'embedding') -> List[List[Any]]:
+    """Batched ``_objects_embedding_search``: one corpus pass answers all queries.  This is what the
+    ingest-time duplicate check needs - ``MergeQuestionsStep.run``
+    (assistant/processing/documents/steps/questions.py:121-126) issues one top-1 search per new
+    question against the same filtered queryset; here the whole document's questions go in one call."""
+    if not query_embeddings:
+        return []
+    return await asyncio.to_thread(_search_many_sync, query_embeddings, qs, n, field)
+
+
 def aggregate_documents(top_objects: Sequence[Any], max_scores_n: int, top_n: int) -> List[Tuple[int, float]]:
     """search_service.py:133-150 without the ORM fetch: group hits by ``document_id`` in rank order,
     keep documents with at least ``max_scores_n`` hits, score ``1 - mean(first max_scores_n

@@ -192,3 +192,21 @@ def test_doc_aggregate_kernel_matches_oracle(n, max_scores_n, top_n):
         assert [d for d, _ in got] == [d for d, _ in want], (q, got, want)
         np.testing.assert_allclose([s for _, s in got], [s for _, s in want], atol=2e-6)
         assert (docs[q][len(want):] == -1).all()
+
+
+def test_embedding_search_many_is_the_batched_dedup_query(table):
+    """One call answers the per-question top-1 searches of MergeQuestionsStep (questions.py:121-139)."""
+    from dab_b200 import search_service as ss
+    T = table._test
+    new_q = T["emb"][[5, 700, 2500]] + 0.01 * np.random.default_rng(9).standard_normal((3, 768)).astype(np.float32)
+    qs = ss.ChunkQuerySet(table).filter(document__id__lt=30)          # "older documents only"
+    got = asyncio.run(ss.embedding_search_many(new_q.tolist(), qs, n=1))
+    allow = T["docs"] < 30
+    S = search_ref.exact_scores(T["emb"], new_q)
+    for i in range(3):
+        want, wsc = search_ref.rank_topk(S[i], 1, allow)
+        assert len(got[i]) == 1 and got[i][0].id == T["pks"][want[0]]
+        assert got[i][0].distance == pytest.approx(1 - wsc[0], abs=2e-6)
+        single = asyncio.run(ss.embedding_search_questions(new_q[i].tolist(), qs, n=1))
+        assert single[0].id == got[i][0].id
+    assert asyncio.run(ss.embedding_search_many([], qs)) == []
