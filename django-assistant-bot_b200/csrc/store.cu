@@ -6,6 +6,7 @@
 // dab_store_search is what `_objects_embedding_search` (assistant/rag/services/
 // search_service.py:185-196) becomes: exact cosine top-k, (score desc, row asc).
 #include <stdlib.h>
+#include <string.h>
 
 #include <atomic>
 #include <mutex>
@@ -59,6 +60,11 @@ struct dab_store {
     void *umma_maps = nullptr;  // tensor maps of the tcgen05 path (built lazily)
     dab_profile prof;
     dab::SearchCtrl *status_host = nullptr;  // pinned landing buffer of dab_store_search_status
+    // staging of dab_store_search_host (allocated on first use): pinned host + device buffers for one
+    // chunk of DAB_MAX_QUERY_BATCH queries and their DAB_MAX_K results
+    void *io_host = nullptr;
+    void *io_dev = nullptr;
+    std::mutex io_mu;  // one host-buffer search at a time per store (they share the staging buffers)
     std::mutex mu;
 };
 
@@ -191,6 +197,8 @@ extern "C" DAB_API void dab_store_destroy(dab_store *s) {
     cudaFree(s->ids);
     cudaFree(s->scratch_base);
     if (s->status_host) cudaFreeHost(s->status_host);
+    if (s->io_host) cudaFreeHost(s->io_host);
+    cudaFree(s->io_dev);
     delete s;
 }
 
@@ -483,4 +491,80 @@ extern "C" DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *
 extern "C" DAB_API const int *dab_store_status_dev(dab_store *s) {
     if (!s) return nullptr;
     return &s->scratch.ctrl->sticky_incomplete;
+}
+
+// ---------------------------------------------------------------- host-buffer search (the e2e entry point)
+namespace dab {
+struct IoLayout {
+    size_t q, scores, ids, total;
+};
+static IoLayout io_layout(int dim) {
+    IoLayout l;
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    l.q = 0;
+    l.scores = up((size_t)DAB_MAX_QUERY_BATCH * dim * sizeof(float));
+    l.ids = l.scores + up((size_t)DAB_MAX_QUERY_BATCH * DAB_MAX_K * sizeof(float));
+    l.total = l.ids + up((size_t)DAB_MAX_QUERY_BATCH * DAB_MAX_K * sizeof(int64_t));
+    return l;
+}
+}  // namespace dab
+
+extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, int Q, int k, const uint32_t *allow_bitmap_dev,
+                                             float *out_scores_host, int64_t *out_ids_host, void *stream) {
+    if (int rc = check_store(s, "dab_store_search_host")) return rc;
+    if (Q < 0) return fail(DAB_E_INVALID, "dab_store_search_host: Q < 0");
+    if (k < 1 || k > DAB_MAX_K) return fail(DAB_E_INVALID, "dab_store_search_host: k must be in 1..DAB_MAX_K");
+    if (Q == 0) return DAB_OK;
+    if (!q_host || !out_scores_host || !out_ids_host) return fail(DAB_E_INVALID, "dab_store_search_host: NULL pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const IoLayout L = io_layout(s->dim);
+    std::lock_guard<std::mutex> io_guard(s->io_mu);
+    {
+        std::lock_guard<std::mutex> g(s->mu);
+        DAB_CUDA_OK(cudaSetDevice(s->device));
+        if (!s->io_host) {
+            DAB_CUDA_OK(cudaHostAlloc(&s->io_host, L.total, cudaHostAllocDefault));
+            DAB_CUDA_OK(cudaMalloc(&s->io_dev, L.total));
+        }
+    }
+    char *hbase = static_cast<char *>(s->io_host), *dbase = static_cast<char *>(s->io_dev);
+    const int saved_spare = s->spare_rounds, saved_path = s->path;
+    int rc = DAB_OK;
+    for (int q0 = 0; q0 < Q && rc == DAB_OK; q0 += DAB_MAX_QUERY_BATCH) {
+        const int nq = Q - q0 < DAB_MAX_QUERY_BATCH ? Q - q0 : DAB_MAX_QUERY_BATCH;
+        const size_t qbytes = (size_t)nq * s->dim * sizeof(float);
+        memcpy(hbase + L.q, q_host + (size_t)q0 * s->dim, qbytes);
+        int spare = 0;
+        bool forced = false;
+        for (;;) {
+            if ((rc = cudaMemcpyAsync(dbase + L.q, hbase + L.q, qbytes, cudaMemcpyHostToDevice, st)) != cudaSuccess) {
+                rc = fail(DAB_E_CUDA, std::string("dab_store_search_host: H2D: ") + cudaGetErrorString((cudaError_t)rc));
+                break;
+            }
+            rc = dab_store_search(s, reinterpret_cast<const float *>(dbase + L.q), nq, k, allow_bitmap_dev,
+                                  reinterpret_cast<float *>(dbase + L.scores), reinterpret_cast<int64_t *>(dbase + L.ids), st);
+            if (rc != DAB_OK) break;
+            cudaMemcpyAsync(hbase + L.scores, dbase + L.scores, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, st);
+            cudaMemcpyAsync(hbase + L.ids, dbase + L.ids, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
+            rc = dab_store_search_status(s, st);   // synchronises the stream: results and verdict are on the host
+            if (rc == DAB_E_INEXACT && !forced) {   // answer this call on the exact CUDA-core path
+                forced = true;
+                s->path = 1;
+                continue;
+            }
+            if (rc == DAB_E_INCOMPLETE && spare < 64) {   // adversarial row order: retry with spare rounds
+                spare = spare == 0 ? 4 : spare * 2;
+                s->spare_rounds = spare;
+                continue;
+            }
+            break;
+        }
+        s->spare_rounds = saved_spare;
+        s->path = saved_path;
+        if (rc == DAB_OK) {
+            memcpy(out_scores_host + (size_t)q0 * k, hbase + L.scores, (size_t)nq * k * sizeof(float));
+            memcpy(out_ids_host + (size_t)q0 * k, hbase + L.ids, (size_t)nq * k * sizeof(int64_t));
+        }
+    }
+    return rc;
 }

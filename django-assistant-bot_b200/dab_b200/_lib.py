@@ -34,6 +34,7 @@ SIGNATURES = {
     "dab_store_append": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_void_p]),
     "dab_store_set_id_base": (c_int, [c_void_p, c_int64]),
     "dab_store_search": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dab_store_search_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dab_store_search_status": (c_int, [c_void_p, c_void_p]),
     "dab_store_set_spare_rounds": (c_int, [c_void_p, c_int]),
     "dab_store_set_path": (c_int, [c_void_p, c_int]),

@@ -201,6 +201,31 @@ class ChunkStore:
                                          _stream(self.device)))
         return scores, ids
 
+    def search_host(self, queries, k: int, allow_bitmap: Optional[torch.Tensor] = None):
+        """Host buffers in, host buffers out: ``queries`` is a float32 NumPy array (or anything
+        ``np.asarray`` accepts, e.g. the Python list the reference passes) of shape [Q, dim] or [dim];
+        returns NumPy ``(scores [Q,k] float32, ids [Q,k] int64)``.  One C call does the copies, the
+        search, the verdict check and any retry."""
+        import numpy as np
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        if q.ndim != 2 or q.shape[1] != self.dim:
+            raise DabError(_lib.DAB_E_DIM, f"different vector dimensions {q.shape[-1]} and {self.dim}")
+        Q = q.shape[0]
+        scores = np.empty((Q, k), dtype=np.float32)
+        ids = np.empty((Q, k), dtype=np.int64)
+        aptr = None
+        if allow_bitmap is not None:
+            _need_cuda(allow_bitmap, "allow_bitmap")
+            if allow_bitmap.numel() * 32 < len(self):
+                raise DabError(_lib.DAB_E_INVALID, "allow bitmap shorter than the store")
+            aptr = allow_bitmap.data_ptr()
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_search_host(self._h, q.ctypes.data, Q, int(k), aptr, scores.ctypes.data, ids.ctypes.data,
+                                              _stream(self.device)))
+        return scores, ids
+
     def search(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None):
         """Checked search: runs ``search_async``, waits, and if a scan round overflowed its
         candidate buffer (adversarial row order) repeats with spare rounds until complete."""

@@ -143,17 +143,16 @@ class DeviceTable:
 
     def search_rows(self, query_embeddings, n: int, bitmap: Optional[torch.Tensor] = None):
         """(distances [Q, n'] float64 ascending, store rows [Q, n'] int64); n' <= n."""
-        q = torch.as_tensor(np.asarray(query_embeddings, dtype=np.float32))
-        if q.dim() == 1:
+        q = np.asarray(query_embeddings, dtype=np.float32)
+        if q.ndim == 1:
             q = q[None]
         if q.shape[-1] != self.dim:
             raise DabError(3, f"different vector dimensions {q.shape[-1]} and {self.dim}")
         if len(self) == 0 or n <= 0:
             return np.zeros((q.shape[0], 0)), np.zeros((q.shape[0], 0), dtype=np.int64)
         k = min(int(n), ops._lib.DAB_MAX_K)
-        scores, ids = self.store.search(q.to(self.device), k, bitmap)
-        scores, ids = scores.cpu().numpy().astype(np.float64), ids.cpu().numpy()
-        return 1.0 - scores, ids
+        scores, ids = self.store.search_host(q, k, bitmap)      # one C call: H2D, search, D2H, verdict, retries
+        return 1.0 - scores.astype(np.float64), ids
 
     def search_documents(self, query_embedding, n: int, max_scores_n: int, top_n: int,
                          bitmap: Optional[torch.Tensor] = None) -> List[Tuple[int, float]]:

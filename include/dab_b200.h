@@ -131,6 +131,15 @@ DAB_API int dab_store_set_id_base(dab_store *s, int64_t id_base);
  */
 DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
                      float *out_scores_dev, int64_t *out_ids_dev, void *stream);
+/*
+ * The same search with HOST buffers, complete and checked: what the reference-facing call uses
+ * (`_objects_embedding_search` receives the query as a Python list, search_service.py:186).
+ * Copies the queries to the device (pinned staging owned by the store, allocated on first use),
+ * searches, copies scores/ids back, synchronises `stream`, and repeats internally if the device
+ * reported DAB_E_INCOMPLETE (spare rounds) or DAB_E_INEXACT (CUDA-core path).  Synchronous.
+ */
+DAB_API int dab_store_search_host(dab_store *s, const float *q_host, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
+                                  float *out_scores_host, int64_t *out_ids_host, void *stream);
 /* Synchronises `stream`; DAB_OK, DAB_E_INCOMPLETE or DAB_E_INEXACT for the last search call on `s`
  * (all of its query chunks). */
 DAB_API int dab_store_search_status(dab_store *s, void *stream);

@@ -116,3 +116,41 @@ def test_randomised_shapes_against_oracle():
         scores, ids = store.search(queries.to(DEV), k)
         _oracle_check(rows.to(dtype).float().numpy(), queries.numpy(), ids.cpu().numpy(), scores.cpu().numpy(), k)
         store.close()
+
+
+def test_search_host_matches_device_search_and_retries():
+    """dab_store_search_host: NumPy in/out through one C call, same answer as the tensor API,
+    including the internal retry on an adversarial corpus."""
+    from dab_b200 import DabError, ops
+    g = torch.Generator().manual_seed(8)
+    N, D, Q, k = 40_000, 768, 300, 12                      # > 256 queries: two chunks inside the C call
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    for dtype in (torch.float32, torch.bfloat16):
+        store = ops.ChunkStore(N, D, dtype, DEV)
+        store.append(rows.to(DEV))
+        hs, hi = store.search_host(queries.numpy(), k)
+        ds, di = store.search(queries.to(DEV), k)
+        np.testing.assert_array_equal(hi, di.cpu().numpy())
+        np.testing.assert_array_equal(hs, ds.cpu().numpy())
+        s1, i1 = store.search_host(queries[0].tolist(), 3)   # a Python list, like the reference passes
+        assert s1.shape == (1, 3) and (i1[0] == hi[0, :3]).all()
+        with pytest.raises(DabError, match="different vector dimensions"):
+            store.search_host(np.zeros(5, np.float32), 3)
+        store.close()
+    # adversarial corpus (see test_gpu_search.py): the C call must retry internally
+    N, D = 300_000, 64
+    rows = torch.randn(N, D, generator=g)
+    q = torch.randn(1, D, generator=g)
+    store = ops.ChunkStore(N, D, torch.float32, DEV)
+    store.append(rows.to(DEV))
+    plan = store.describe_plan(1, 10)
+    r = torch.arange(100_000, 130_000)
+    r = r[(r // plan["tile_rows"]) % plan["strides"][-2] != 0]
+    rows[r] = q + 0.05 * torch.randn(r.numel(), D, generator=g)
+    store.reset()
+    store.append(rows.to(DEV))
+    hs, hi = store.search_host(q.numpy(), 10)
+    S = search_ref.exact_scores(rows.numpy(), q.numpy())
+    search_ref.check_topk_parity(S[0], hi[0], hs[0], 10)
+    store.close()
