@@ -210,3 +210,37 @@ def test_embedding_search_many_is_the_batched_dedup_query(table):
         single = asyncio.run(ss.embedding_search_questions(new_q[i].tolist(), qs, n=1))
         assert single[0].id == got[i][0].id
     assert asyncio.run(ss.embedding_search_many([], qs)) == []
+
+
+def test_c1_reference_cpu_path_shape_end_to_end():
+    """BASELINE config[0]: 32 chunks x 256 tokens through a MiniLM-L6-shaped 384-d encoder (random init),
+    mean-pool + L2 norm, exact cosine top-10 over 10k chunks - the whole hot path on the device against
+    the oracle (pool: masked mean of the same hidden states; retrieve: float64 cosine ranking)."""
+    from transformers import BertConfig, BertModel
+    from dab_b200 import ops
+    torch.manual_seed(0)
+    cfg = BertConfig(vocab_size=30522, hidden_size=384, num_hidden_layers=6, num_attention_heads=12,
+                     intermediate_size=1536, max_position_embeddings=512)
+    model = BertModel(cfg).eval().to(DEV)
+    g = torch.Generator().manual_seed(555)
+    B, T = 32, 256
+    ids = torch.randint(1000, 30000, (B, T), generator=g)
+    lengths = torch.randint(16, T + 1, (B,), generator=g)
+    mask = (torch.arange(T)[None] < lengths[:, None]).long()
+    with torch.no_grad():
+        hidden = model(input_ids=ids.to(DEV), attention_mask=mask.to(DEV)).last_hidden_state
+    emb = ops.pool_l2norm(hidden, mask.to(DEV))
+    want, _ = pool_ref.masked_mean_pool(hidden.float().cpu().numpy(), mask.numpy())
+    np.testing.assert_allclose(emb.cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+    # the 10k-chunk store: 32 embedded chunks + random unit vectors, queried with the chunks themselves
+    N = 10_000
+    corpus = torch.nn.functional.normalize(torch.randn(N, 384, generator=g), dim=1)
+    corpus[:B] = emb.cpu()
+    store = ops.ChunkStore(N, 384, torch.float32, DEV)
+    store.append(corpus.to(DEV))
+    scores, rows = store.search(emb, 10)
+    S = search_ref.exact_scores(corpus.numpy(), emb.cpu().numpy())
+    for q in range(B):
+        search_ref.check_topk_parity(S[q], rows[q].cpu().numpy(), scores[q].cpu().numpy(), 10)
+        assert rows[q, 0].item() == q and abs(scores[q, 0].item() - 1.0) < 1e-5       # each chunk finds itself first
+    store.close()
