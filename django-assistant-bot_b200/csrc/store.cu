@@ -568,3 +568,46 @@ extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, 
     }
     return rc;
 }
+
+// ---------------------------------------------------------------- maintenance: tombstones and export
+namespace dab {
+namespace {
+__global__ void delete_rows_kernel(float *__restrict__ inv_norm, const int64_t *__restrict__ rows, int64_t n, int64_t size) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const int64_t r = rows[i];
+        if (r >= 0 && r < size) inv_norm[r] = 0.f;   // a row with inverse norm 0 is never returned by any scan
+    }
+}
+}  // namespace
+}  // namespace dab
+
+extern "C" DAB_API int dab_store_delete_rows(dab_store *s, const int64_t *rows_dev, int64_t n, void *stream) {
+    if (int rc = check_store(s, "dab_store_delete_rows")) return rc;
+    if (n < 0 || (n > 0 && !rows_dev)) return fail(DAB_E_INVALID, "dab_store_delete_rows: bad argument");
+    if (n == 0) return DAB_OK;
+    std::lock_guard<std::mutex> g(s->mu);
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    delete_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(s->inv_norm, rows_dev, n, s->size);
+    DAB_LAUNCH_OK();
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_export(dab_store *s, int64_t row0, int64_t n, void *rows_out_dev, float *inv_norm_out_dev,
+                                        int64_t *ids_out_dev, void *stream) {
+    if (int rc = check_store(s, "dab_store_export")) return rc;
+    std::lock_guard<std::mutex> g(s->mu);
+    if (row0 < 0 || n < 0 || row0 + n > s->size) return fail(DAB_E_INVALID, "dab_store_export: row range outside the store");
+    if (n == 0) return DAB_OK;
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t row_bytes = (size_t)s->dim * (s->dtype == DAB_BF16 ? 2 : 4);
+    if (rows_out_dev)
+        DAB_CUDA_OK(cudaMemcpyAsync(rows_out_dev, static_cast<char *>(s->rows) + (size_t)row0 * row_bytes, (size_t)n * row_bytes,
+                                    cudaMemcpyDeviceToDevice, st));
+    if (inv_norm_out_dev)
+        DAB_CUDA_OK(cudaMemcpyAsync(inv_norm_out_dev, s->inv_norm + row0, (size_t)n * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (ids_out_dev)
+        DAB_CUDA_OK(cudaMemcpyAsync(ids_out_dev, s->ids + row0, (size_t)n * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+    return DAB_OK;
+}

@@ -173,6 +173,23 @@ class ChunkStore:
             check(lib().dab_store_append(self._h, rows.data_ptr(), _DTYPES[rows.dtype], iptr, rows.shape[0],
                                          _stream(self.device)))
 
+    def delete_rows(self, rows: torch.Tensor) -> None:
+        """Tombstone store rows (row indices, not ids): they are never returned again."""
+        _need_cuda(rows, "rows")
+        rows = rows.to(torch.int64).contiguous()
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_delete_rows(self._h, rows.data_ptr(), rows.numel(), _stream(self.device)))
+
+    def export(self, row0: int, n: int):
+        """(rows [n,dim] in the store's dtype, inv_norm [n] fp32, ids [n] int64) copied out of the store."""
+        rows = torch.empty((n, self.dim), dtype=self.dtype, device=self.device)
+        inv = torch.empty((n,), dtype=torch.float32, device=self.device)
+        ids = torch.empty((n,), dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_export(self._h, int(row0), int(n), rows.data_ptr(), inv.data_ptr(), ids.data_ptr(),
+                                         _stream(self.device)))
+        return rows, inv, ids
+
     # -- read side
     def search_async(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None,
                      out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):

@@ -86,6 +86,7 @@ class DeviceTable:
         self._cols: Dict[str, np.ndarray] = {}
         self._row_of_pk: Dict[int, int] = {}
         self._doc_dev: Optional[torch.Tensor] = None     # device copy of the document_id column (lazy)
+        self._deleted: set = set()                        # store rows turned into tombstones
         self.documents: Dict[int, Any] = {}
 
     def __len__(self):
@@ -117,6 +118,60 @@ class DeviceTable:
         for k, v in meta.items():
             self._meta.setdefault(k, []).extend(list(v))
         self._cols.clear()
+
+    def delete(self, pks: Iterable[int]) -> int:
+        """Remove rows by pk: what ``Document.objects.filter(...).delete()`` cascades to on finalisation
+        (assistant/processing/tasks.py:67-74).  Rows become tombstones on the device (never returned
+        again) and are masked out of every later queryset; returns how many rows were removed."""
+        rows = [self._row_of_pk.pop(int(p)) for p in pks if int(p) in self._row_of_pk]
+        if not rows:
+            return 0
+        self.store.delete_rows(torch.as_tensor(rows, dtype=torch.int64).to(self.device))
+        self._deleted.update(rows)
+        self._cols.clear()
+        return len(rows)
+
+    def live_mask(self) -> Optional[np.ndarray]:
+        if not self._deleted:
+            return None
+        m = np.ones(len(self), dtype=np.bool_)
+        m[list(self._deleted)] = False
+        return m
+
+    def save(self, path: str) -> None:
+        """Snapshot of the shard: rows in the store's dtype + the host columns, as one ``.npz``.
+        The device store is a cache of the DB column (it can always be rebuilt from PostgreSQL);
+        the snapshot only avoids re-reading and re-uploading 768 floats per row at start-up."""
+        n = len(self)
+        blocks = []
+        for r0 in range(0, n, 1 << 18):
+            rows, _, _ = self.store.export(r0, min(1 << 18, n - r0))
+            blocks.append(rows.view(torch.int16).cpu().numpy() if rows.dtype == torch.bfloat16 else rows.cpu().numpy())
+        data = np.concatenate(blocks, 0) if blocks else np.zeros((0, self.dim), np.float32)
+        meta = {f"meta__{k}": np.asarray(v) for k, v in self._meta.items()}
+        np.savez(path, rows=data, bf16=np.asarray(self.store.dtype == torch.bfloat16), dim=np.asarray(self.dim),
+                 pks=np.asarray(self._pks, dtype=np.int64), docs=np.asarray(self._doc, dtype=np.int64),
+                 orders=np.asarray(self._order, dtype=np.int64),
+                 texts=np.asarray(["" if t is None else t for t in self._text], dtype=object),
+                 deleted=np.asarray(sorted(self._deleted), dtype=np.int64), **meta)
+
+    @classmethod
+    def load(cls, path: str, capacity: Optional[int] = None, device=None) -> "DeviceTable":
+        z = np.load(path, allow_pickle=True)
+        bf16 = bool(z["bf16"])
+        n = z["rows"].shape[0]
+        t = cls(max(capacity or n, 1), int(z["dim"]), torch.bfloat16 if bf16 else torch.float32, device)
+        meta = {k[len("meta__"):]: z[k] for k in z.files if k.startswith("meta__")}
+        for r0 in range(0, n, 1 << 18):
+            r1 = min(n, r0 + (1 << 18))
+            blk = torch.from_numpy(z["rows"][r0:r1])
+            emb = blk.view(torch.bfloat16) if bf16 else blk
+            t.add(z["pks"][r0:r1].tolist(), emb, z["docs"][r0:r1].tolist(), [x or None for x in z["texts"][r0:r1].tolist()],
+                  z["orders"][r0:r1].tolist(), **{k: v[r0:r1] for k, v in meta.items()})
+        dead = z["deleted"].tolist()
+        if dead:
+            t.delete([t._pks[r] for r in dead])
+        return t
 
     def column(self, name: str) -> np.ndarray:
         if name not in self._cols:
@@ -201,7 +256,11 @@ class ChunkQuerySet:
         self._mask = mask
 
     def _apply(self, kwargs, negate: bool) -> "ChunkQuerySet":
-        mask = np.ones(len(self.table), dtype=np.bool_) if self._mask is None else self._mask.copy()
+        if self._mask is not None:
+            mask = self._mask.copy()
+        else:
+            live = self.table.live_mask() if hasattr(self.table, "live_mask") else None
+            mask = np.ones(len(self.table), dtype=np.bool_) if live is None else live
         for key, value in kwargs.items():
             name, op = key, "exact"
             if "__" in key and key.rsplit("__", 1)[1] in _LOOKUPS:
@@ -221,7 +280,9 @@ class ChunkQuerySet:
         return self
 
     def count(self) -> int:
-        return len(self.table) if self._mask is None else int(self._mask.sum())
+        if self._mask is not None:
+            return int(self._mask.sum())
+        return len(self.table) - len(getattr(self.table, "_deleted", ()))
 
     def allow_bitmap(self) -> Optional[torch.Tensor]:
         return None if self._mask is None else self.table.bitmap_from_mask(self._mask)

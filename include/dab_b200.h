@@ -112,6 +112,19 @@ DAB_API int dab_store_reset(dab_store *s);
  */
 DAB_API int dab_store_append(dab_store *s, const void *rows_dev, int rows_dtype, const int64_t *ids_dev_or_null,
                      int64_t n, void *stream);
+/*
+ * Delete rows (tombstones): the rows stay in place but are never returned again - their stored
+ * inverse norm becomes 0, which every scan treats like a zero vector.  Replaces the deletes of
+ * document finalisation (older documents of a wiki removed, assistant/processing/tasks.py:67-74).
+ *   rows_dev [n] int64 STORE ROW indices (not ids); out-of-range entries are ignored.
+ */
+DAB_API int dab_store_delete_rows(dab_store *s, const int64_t *rows_dev, int64_t n, void *stream);
+/*
+ * Copy rows [row0, row0+n) out of the store, in the store's dtype, with their inverse norms
+ * (0 = deleted / zero row) and ids; any output may be NULL.  For snapshots of a shard.
+ */
+DAB_API int dab_store_export(dab_store *s, int64_t row0, int64_t n, void *rows_out_dev, float *inv_norm_out_dev_or_null,
+                             int64_t *ids_out_dev_or_null, void *stream);
 /* id given to row i when ids are implicit: id_base + i (a shard's first global row index) */
 DAB_API int dab_store_set_id_base(dab_store *s, int64_t id_base);
 

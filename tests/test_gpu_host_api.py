@@ -244,3 +244,40 @@ def test_c1_reference_cpu_path_shape_end_to_end():
         search_ref.check_topk_parity(S[q], rows[q].cpu().numpy(), scores[q].cpu().numpy(), 10)
         assert rows[q, 0].item() == q and abs(scores[q, 0].item() - 1.0) < 1e-5       # each chunk finds itself first
     store.close()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_delete_and_snapshot_roundtrip(tmp_path, dtype):
+    """Tombstoned rows never come back; a saved shard reloads to the same answers."""
+    from dab_b200 import search_service as ss
+    rng = np.random.default_rng(3)
+    n, d = 4000, 768
+    emb = rng.standard_normal((n, d)).astype(np.float32)
+    pks = np.arange(10, 10 + n)
+    docs = rng.integers(1, 40, size=n)
+    t = ss.DeviceTable(n, d, dtype, DEV)
+    t.add(pks, emb, document_ids=docs, texts=[f"s{i}" for i in range(n)], document__wiki__bot=docs % 2)
+    stored = torch.from_numpy(emb).to(dtype).float().numpy()
+    q = rng.standard_normal(d).astype(np.float32)
+    S = search_ref.exact_scores(stored, q)[0]
+    top, _ = search_ref.rank_topk(S, 5)
+    # delete the two best hits and every row of one document (what finalisation does to older documents)
+    gone = set(pks[top[:2]].tolist()) | set(pks[docs == docs[top[2]]].tolist())
+    assert t.delete(gone) == len(gone) and t.delete(gone) == 0
+    alive = ~np.isin(pks, list(gone))
+    qs = ss.ChunkQuerySet(t)
+    assert qs.count() == alive.sum()
+    hits = asyncio.run(ss._objects_embedding_search(q.tolist(), qs, n=20))
+    want, wsc = search_ref.rank_topk(S, 20, alive)
+    assert [h.id for h in hits] == list(pks[want])
+    assert qs.filter(document__wiki__bot=1).count() == (alive & (docs % 2 == 1)).sum()
+    # snapshot -> reload -> same answers, deletions included
+    path = str(tmp_path / "shard.npz")
+    t.save(path)
+    t2 = ss.DeviceTable.load(path, device=DEV)
+    assert len(t2) == n and ss.ChunkQuerySet(t2).count() == alive.sum()
+    hits2 = asyncio.run(ss._objects_embedding_search(q.tolist(), ss.ChunkQuerySet(t2), n=20))
+    assert [h.id for h in hits2] == [h.id for h in hits] and hits2[0].text == hits[0].text
+    np.testing.assert_allclose([h.distance for h in hits2], [h.distance for h in hits], atol=1e-7)
+    t.close()
+    t2.close()
