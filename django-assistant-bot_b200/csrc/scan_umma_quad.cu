@@ -35,6 +35,7 @@ using namespace umma;
 constexpr int kThreads = 256;
 constexpr int kMaxStages = 8;
 constexpr int kMinStages = 3;
+constexpr int kMaxAcc = 4;         // TMEM accumulator stages (512 columns / n_pair, at most 4)
 constexpr int kPendCap = 512;       // staged candidates per accumulator stage per CTA
 constexpr int kSuperRows = 2 * kTileRows;  // corpus rows per MMA pair step (UMMA M = 256)
 constexpr int kSmemBudget = 227 * 1024 - 2048;
@@ -97,7 +98,7 @@ __device__ __forceinline__ void umma_commit_mc2(uint64_t *bar, uint16_t mask) {
 __global__ void __launch_bounds__(kThreads, 1)
 scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
                       const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pair, int stages,
-                      int tmem_cols, int num_pairs, const __grid_constant__ LevelPlan plan) {
+                      int tmem_cols, int num_pairs, int acc_stages, const __grid_constant__ LevelPlan plan) {
     extern __shared__ unsigned char smem_raw[];
     const int lvl = sc.ctrl->cur_level;
     if (lvl >= plan.num_levels) return;
@@ -124,9 +125,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     uint64_t *empty = full + kMaxStages;               // ranks 0/1: both pairs are done with the stage
     uint64_t *b_full = empty + kMaxStages;             // this CTA's query quarter landed
     uint64_t *b_pair = b_full + 1;                     // leaders: both quarters of the pair landed
-    uint64_t *tmem_full = b_pair + 1;                  // [2] accumulator stage complete (both CTAs of the pair)
-    uint64_t *tmem_empty = tmem_full + 2;              // [2] leaders: both CTAs drained the accumulator stage
-    uint64_t *pend_full = tmem_empty + 2;              // [2] all 4 epilogue warps finished appending to list a
+    uint64_t *tmem_full = b_pair + 1;                  // [kMaxAcc] accumulator stage complete (both CTAs of the pair)
+    uint64_t *tmem_empty = tmem_full + kMaxAcc;        // [kMaxAcc] leaders: both CTAs drained the accumulator stage
+    uint64_t *pend_full = tmem_empty + kMaxAcc;              // [2] all 4 epilogue warps finished appending to list a
     uint64_t *pend_free = pend_full + 2;               // [2] the flusher drained list a
     uint64_t *pend_key = pend_free + 2;                // [2][kPendCap]
     uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(pend_key + 2 * kPendCap);
@@ -141,9 +142,11 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         }
         mbar_init(b_full, 1);
         mbar_init(b_pair, 2);
-        for (int a = 0; a < 2; a++) {
+        for (int a = 0; a < kMaxAcc; a++) {
             mbar_init(&tmem_full[a], 1);
             mbar_init(&tmem_empty[a], 8);
+        }
+        for (int a = 0; a < 2; a++) {
             mbar_init(&pend_full[a], 4);
             mbar_init(&pend_free[a], 1);
             pend_n[a] = 0;
@@ -199,8 +202,8 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             int s = 0;
             uint32_t ph = 0;
             for (long long it = 0; it < my_tiles; it++) {
-                const int a = (int)(it & 1);
-                const uint32_t aph = (uint32_t)((it >> 1) & 1);
+                const int a = (int)(it % acc_stages);
+                const uint32_t aph = (uint32_t)((it / acc_stages) & 1);
                 mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(a * n_pair);
@@ -250,15 +253,17 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         long long row = row_of(0);
         float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
         for (long long it = 0; it < my_tiles; it++) {
-            const int a = (int)(it & 1);
-            const uint32_t aph = (uint32_t)((it >> 1) & 1);
+            const int a = (int)(it % acc_stages);                  // accumulator stage
+            const uint32_t aph = (uint32_t)((it / acc_stages) & 1);
+            const int pl = (int)(it & 1);                           // staging list (always two)
+            const uint32_t plph = (uint32_t)((it >> 1) & 1);
             const long long row_next = it + 1 < my_tiles ? row_of(it + 1) : sv.n;
             const float rinv_next = row_next < sv.n ? sv.inv_norm[row_next] : 0.f;
-            mbar_wait_bounded(&pend_free[a], aph ^ 1u);       // the flusher is done with list a (tile it-2)
+            mbar_wait_bounded(&pend_free[pl], plph ^ 1u);     // the flusher is done with this list (tile it-2)
             mbar_wait_bounded(&tmem_full[a], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair);
-            const PendList pend = {pend_key + a * kPendCap, pend_q + a * kPendCap, pend_n + a, kPendCap};
+            const PendList pend = {pend_key + pl * kPendCap, pend_q + pl * kPendCap, pend_n + pl, kPendCap};
             epilogue_tile(taddr, (nq + 15) & ~15, rinv, row, tau_s, q0, allow, sc, &pend);
             row = row_next;
             rinv = rinv_next;
@@ -266,7 +271,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             __syncwarp();
             if (lane == 0) {
                 if (leader) mbar_arrive(&tmem_empty[a]); else mbar_arrive_remote(&tmem_empty[a], rank & ~1u);
-                mbar_arrive(&pend_full[a]);
+                mbar_arrive(&pend_full[pl]);
             }
         }
     }
@@ -289,13 +294,13 @@ bool plan_quad(int dim, int nq, int num_pairs, QuadPlan *out) {
     if (n_pair < 32) n_pair = 32;
     if (n_pair > 128) return false;
     const size_t b_bytes = (size_t)(n_pair / 2) * dim * 2;
-    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 12) * sizeof(uint64_t) + 16 +
+    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 +
                          2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
     int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
     if (stages > kMaxStages) stages = kMaxStages;
-    int cols = 32;
-    while (cols < 2 * n_pair) cols <<= 1;
+    // all 512 TMEM columns: as many accumulator stages as fit (2..4) decouple the MMAs from epilogue jitter
+    int cols = 512;
     out->n_pair = n_pair;
     out->stages = stages;
     out->tmem_cols = cols;
@@ -354,13 +359,16 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long clusters = max_tiles < max_clusters ? max_tiles : max_clusters;
+    int acc = qp.tmem_cols / qp.n_pair;
+    if (acc > kMaxAcc) acc = kMaxAcc;
+    if (const char *e = getenv("DAB_QUAD_ACC")) acc = atoi(e) >= 2 && atoi(e) <= acc ? atoi(e) : acc;  // tuning aid
     static const bool debug = getenv("DAB_DEBUG") != nullptr;
     if (debug)
         fprintf(stderr, "[dab] quad: pairs=%d nq=%d n_pair=%d stages=%d tmem_cols=%d smem=%zu max_clusters=%d clusters=%lld levels=%d\n", num_pairs, nq,
                 qp.n_pair, qp.stages, qp.tmem_cols, qp.smem, max_clusters, clusters, plan.num_levels);
     cfg.gridDim = dim3((unsigned)(clusters * kCluster), 1, 1);
     DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, scan_umma_quad_kernel, tmap_rows, tmap_q, sv, allow, sc, q0, nq, qp.n_pair, qp.stages,
-                                   qp.tmem_cols, num_pairs, plan));
+                                   qp.tmem_cols, num_pairs, acc, plan));
     count_launch();
     return DAB_OK;
 }
