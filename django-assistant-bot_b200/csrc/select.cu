@@ -144,6 +144,107 @@ __device__ void bitonic_sort_desc(uint64_t *keys, int P) {
 }
 
 constexpr int kCompactThreads = 1024;
+constexpr int kSelBins = 2 * kCompactThreads;  // two histogram bins per thread
+
+// Selection instead of sorting (tensor path, ordinary rounds).  `keys` is the shared-memory copy
+// buffer, `mine` the query's candidate list in global memory (n entries, n >= k).  On success the
+// kept candidates (every key whose score is >= [lower edge of the histogram bin that holds the k-th
+// best score, minus one bin, minus margin]) are compacted into mine[0..kept) in index order, the
+// count and the threshold are published and true is returned.  Returns false (block-uniform, nothing
+// modified) when the scores are degenerate or the kept set would exceed k_cap: the caller then takes
+// the exact sort path.
+__device__ bool compact_select(uint64_t *keys, uint64_t *mine, int n, int k, int k_cap, float margin, uint32_t *cand_count,
+                               uint64_t *tau_key) {
+    __shared__ int s_hist[kSelBins];
+    __shared__ float s_min[kCompactThreads / 32], s_max[kCompactThreads / 32];
+    __shared__ int s_part[kCompactThreads / 32];
+    __shared__ int s_bstar;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float lo = INFINITY, hi = -INFINITY;
+    for (int i = tid; i < n; i += kCompactThreads) {
+        const uint64_t key = mine[i];
+        keys[i] = key;
+        const float s = key_score(key);
+        lo = fminf(lo, s);
+        hi = fmaxf(hi, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if (lane == 0) {
+        s_min[warp] = lo;
+        s_max[warp] = hi;
+    }
+    for (int b = tid; b < kSelBins; b += kCompactThreads) s_hist[b] = 0;
+    __syncthreads();
+    lo = s_min[0];
+    hi = s_max[0];
+    for (int w = 1; w < kCompactThreads / 32; w++) {
+        lo = fminf(lo, s_min[w]);
+        hi = fmaxf(hi, s_max[w]);
+    }
+    if (!(hi > lo) || !(hi - lo < INFINITY)) return false;
+    const float scale = (float)kSelBins / (hi - lo);
+    for (int i = tid; i < n; i += kCompactThreads) {
+        const int b = min(kSelBins - 1, max(0, (int)((key_score(keys[i]) - lo) * scale)));
+        atomicAdd(&s_hist[b], 1);
+    }
+    __syncthreads();
+    // suffix counts from the top bin down: thread t owns bins 2p and 2p+1 with p = last - t
+    const int p = kCompactThreads - 1 - tid;
+    const int h0 = s_hist[2 * p], h1 = s_hist[2 * p + 1];
+    int incl = h0 + h1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_part[warp] = incl;
+    __syncthreads();
+    int before = 0;
+    for (int w = 0; w < warp; w++) before += s_part[w];
+    incl += before;                     // keys in bins >= 2p
+    const int excl = incl - (h0 + h1);  // keys in bins > 2p+1
+    if (excl < k && k <= incl) s_bstar = (excl + h1 >= k) ? 2 * p + 1 : 2 * p;
+    __syncthreads();
+    const float thr = lo + (float)(s_bstar - 1) / scale - margin;
+    const uint64_t thr_key = make_key(thr, 0xffffffffu);
+    // first count, then (only if it fits) compact: a refused call must leave mine[] untouched
+    int kept = 0;
+    for (int i = tid; i < n; i += kCompactThreads) kept += keys[i] > thr_key ? 1 : 0;
+    kept = __reduce_add_sync(0xffffffffu, kept);
+    __syncthreads();                    // s_part is reused
+    if (lane == 0) s_part[warp] = kept;
+    __syncthreads();
+    kept = 0;
+    for (int w = 0; w < kCompactThreads / 32; w++) kept += s_part[w];
+    if (kept > k_cap) return false;
+    int done = 0;
+    for (int base = 0; base < n; base += kCompactThreads) {
+        const int i = base + tid;
+        const uint64_t me = i < n ? keys[i] : 0ull;
+        const int flag = (i < n && me > thr_key) ? 1 : 0;
+        const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+        __syncthreads();
+        if (lane == 0) s_part[warp] = __popc(ballot);
+        __syncthreads();
+        int offset = done, block_total = 0;
+        for (int w = 0; w < kCompactThreads / 32; w++) {
+            const int c = s_part[w];
+            if (w < warp) offset += c;
+            block_total += c;
+        }
+        if (flag) mine[offset + __popc(ballot & ((1u << lane) - 1u))] = me;
+        done += block_total;
+    }
+    if (tid == 0) {
+        *cand_count = (uint32_t)kept;
+        *tau_key = thr_key;
+    }
+    return true;
+}
 
 // One CTA per query: sort this round's candidates, drop duplicates (a retried level re-adds
 // rows), keep the best k_keep, publish the new threshold; the last CTA to finish advances
@@ -161,9 +262,20 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
         const uint32_t raw = sc.cand_count[qi];
         const int n = (int)min(raw, (uint32_t)kCandCap);
         const bool ovf = raw > (uint32_t)kCandCap;
+        uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
+        // Tensor path, ordinary round: nothing here needs ORDER, only "the k-th best score, minus the
+        // margin, as a threshold" - and any threshold at or below that is still correct (it keeps a
+        // superset).  So select instead of sort: histogram of the scores, the bin where the k-th best
+        // falls, its lower edge (one bin of slack) minus the margin.  Falls back to the exact sort
+        // path below when the round overflowed or is a retry (duplicates), when fewer than k
+        // candidates exist, or when the kept set would not fit.
+        bool fast_done = false;
+        if (margin > 0.f && !ovf && !ctrl->retry && n >= k) {
+            fast_done = compact_select(keys, mine, n, k, k_cap, margin, &sc.cand_count[qi], &sc.tau_key[qi]);
+        }
+        if (!fast_done) {
         int P = 32;
         while (P < n) P <<= 1;
-        uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
         for (int i = tid; i < P; i += kCompactThreads) keys[i] = i < n ? mine[i] : 0ull;
         bitonic_sort_desc<kCompactThreads>(keys, P);
         // dedupe + keep the first k_cap unique keys (block-wide exclusive scan of the "is new" flags)
@@ -219,6 +331,7 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
             __syncthreads();
             if (tid == 0) sc.cand_count[qi] = s_keep;
         }
+        }  // !fast_done
         if (tid == 0) {
             sc.overflowed[qi] = ovf ? 1 : 0;
             if (ovf) atomicExch(&ctrl->any_overflow, 1);
