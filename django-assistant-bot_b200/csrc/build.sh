@@ -8,7 +8,7 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompil
        --expt-relaxed-constexpr -Xptxas -v)
 mkdir -p obj
 pids=()
-for f in pool.cu select.cu scan_simt.cu scan_umma.cu scan_umma_quad.cu store.cu noalloc.cu exchange.cu docagg.cu; do
+for f in pool.cu select.cu scan_simt.cu scan_umma.cu scan_umma_quad.cu scan_umma_qa.cu store.cu noalloc.cu exchange.cu docagg.cu; do
   [ -f "$f" ] || continue
   o=obj/${f%.cu}.o
   if [ ! -f "$o" ] || [ "$f" -nt "$o" ] || [ common.cuh -nt "$o" ] || [ search.cuh -nt "$o" ] || [ umma.cuh -nt "$o" ] || [ ../../include/dab_b200.h -nt "$o" ]; then

@@ -298,6 +298,7 @@ struct ScanTimer {
 struct SearchPlan {
     int path;        // 1 = CUDA cores, 2 = tcgen05
     bool quad;       // tcgen05: 4-CTA cluster kernel for wide query blocks
+    bool qa;         // tcgen05: queries-as-A pair kernel for wide query blocks (preferred when it applies)
     int k_cap;       // candidates kept per query between levels
     float margin;    // tensor path: approximate-score margin that is kept for rescoring
     LevelPlan levels;
@@ -317,9 +318,13 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
         sp.k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // wide blocks that do not fit one SM's shared memory go to the 4-CTA cluster kernel
         static const bool no_quad = getenv("DAB_NO_QUAD") != nullptr;  // tuning aid: use query-slice groups instead
-        sp.quad = !no_quad && nq > umma_queries_per_pass(dim) && quad_supported(dim, dtype, nq);
+        static const bool no_qa = getenv("DAB_NO_QA") != nullptr;      // tuning aid: fall back to the cluster kernel
+        const bool wide = nq > umma_queries_per_pass(dim);
+        sp.qa = wide && !no_qa && qa_supported(dim, dtype, nq);
+        sp.quad = wide && !sp.qa && !no_quad && quad_supported(dim, dtype, nq);
         // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
-        sp.levels = make_level_plan(n, sp.quad ? quad_tile_rows() : umma_tile_rows(), 4 * k < sp.k_cap ? 4 * k : sp.k_cap);
+        sp.levels = make_level_plan(n, sp.qa ? qa_tile_rows() : sp.quad ? quad_tile_rows() : umma_tile_rows(),
+                                    4 * k < sp.k_cap ? 4 * k : sp.k_cap);
     } else {
         sp.margin = 0.f;
         sp.k_cap = k;
@@ -342,7 +347,9 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
                 // one launch scores all nq queries
                 ScanTimer tm(s->prof, st);
                 static const bool pair_mode = getenv("DAB_WIDE_PAIRS") != nullptr;  // tuning aid
-                if (sp.quad && pair_mode) {
+                if (sp.qa) {
+                    if (int rc = launch_scan_umma_qa(sv, allow, sc, 0, nq, plan, s->num_sms, st)) return rc;
+                } else if (sp.quad && pair_mode) {
                     const int per = pair_queries_per_pass(sv.dim);
                     for (int q0 = 0; q0 < nq; q0 += per)
                         if (int rc = launch_scan_umma_quad(sv, allow, sc, q0, nq - q0 < per ? nq - q0 : per, plan, s->num_sms, st, 1))
@@ -478,7 +485,7 @@ extern "C" DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *
     std::lock_guard<std::mutex> g(s->mu);
     const int nq = Q < DAB_MAX_QUERY_BATCH ? Q : DAB_MAX_QUERY_BATCH;
     const SearchPlan sp = choose_plan(s, s->size > 0 ? s->size : 1, s->dim, s->dtype, nq, k);
-    if (path) *path = sp.path == 2 && sp.quad ? 3 : sp.path;
+    if (path) *path = sp.path == 2 && sp.qa ? 4 : sp.path == 2 && sp.quad ? 3 : sp.path;
     if (tile_rows) *tile_rows = sp.levels.tile_rows;
     if (num_levels) *num_levels = sp.levels.num_levels;
     if (growth) *growth = sp.levels.growth;
