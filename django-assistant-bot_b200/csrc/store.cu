@@ -318,9 +318,10 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
         sp.k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // wide blocks that do not fit one SM's shared memory go to the 4-CTA cluster kernel
         static const bool no_quad = getenv("DAB_NO_QUAD") != nullptr;  // tuning aid: use query-slice groups instead
-        static const bool no_qa = getenv("DAB_NO_QA") != nullptr;      // tuning aid: fall back to the cluster kernel
+        // queries-as-A kernel: parity-green but measured slower than the cluster kernel; opt-in
+        static const bool use_qa = getenv("DAB_USE_QA") != nullptr;
         const bool wide = nq > umma_queries_per_pass(dim);
-        sp.qa = wide && !no_qa && qa_supported(dim, dtype, nq);
+        sp.qa = wide && use_qa && qa_supported(dim, dtype, nq);
         sp.quad = wide && !sp.qa && !no_quad && quad_supported(dim, dtype, nq);
         // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
         sp.levels = make_level_plan(n, sp.qa ? qa_tile_rows() : sp.quad ? quad_tile_rows() : umma_tile_rows(),
