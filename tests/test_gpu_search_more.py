@@ -154,3 +154,45 @@ def test_search_host_matches_device_search_and_retries():
     S = search_ref.exact_scores(rows.numpy(), q.numpy())
     search_ref.check_topk_parity(S[0], hi[0], hs[0], 10)
     store.close()
+
+
+def test_concurrent_searches_from_threads():
+    """The reference reaches the search from an asgiref worker thread while another coroutine runs
+    (context_service/service.py:82-83) and from several uvicorn workers: calls on one store are
+    serialised by the library, calls on different stores are independent; answers must not mix."""
+    import threading
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(13)
+    N, D, k = 30_000, 768, 10
+    rows_a = torch.randn(N, D, generator=g)
+    rows_b = torch.randn(N, D, generator=g)
+    qs = torch.randn(8, D, generator=g)
+    store_a = ops.ChunkStore(N, D, torch.float32, DEV)
+    store_b = ops.ChunkStore(N, D, torch.bfloat16, DEV)
+    store_a.append(rows_a.to(DEV))
+    store_b.append(rows_b.to(DEV))
+    Sa = search_ref.exact_scores(rows_a.numpy(), qs.numpy())
+    Sb = search_ref.exact_scores(rows_b.to(torch.bfloat16).float().numpy(), qs.numpy())
+    errors = []
+
+    def worker(store, S, qi, reps):
+        try:
+            stream = torch.cuda.Stream(device=DEV)
+            with torch.cuda.stream(stream):
+                for _ in range(reps):
+                    s, i = store.search_host(qs[qi].numpy(), k)
+                    search_ref.check_topk_parity(S[qi], i[0], s[0], k)
+                    s2, i2 = store.search(qs[qi:qi + 1].to(DEV), k)
+                    search_ref.check_topk_parity(S[qi], i2[0].cpu().numpy(), s2[0].cpu().numpy(), k)
+        except Exception as e:  # pragma: no cover
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=worker, args=(store_a if t % 2 == 0 else store_b, Sa if t % 2 == 0 else Sb, t, 15))
+               for t in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    store_a.close()
+    store_b.close()
