@@ -44,6 +44,8 @@ WORKLOADS = {
                desc="100M x 768 bf16 store row-sharded over the GPUs, Q=256, top-100 (configs[3])"),
     "c4q64": dict(kind="search", rows=100_000_000, dim=768, dtype="bf16", Q=64, k=100,
                   desc="100M x 768 bf16 store row-sharded over the GPUs, Q=64, top-100 (north_star target)"),
+    "f32q32": dict(kind="search", rows=4_000_000, dim=768, dtype="f32", Q=32, k=10,
+                   desc="4M x 768 fp32 store (what pgvector holds), Q=32, top-10: kind::tf32 tensor pass + fp32 rescoring"),
     "c5": dict(kind="pool", B=256, T=512, dim=1024, dtype="f32",
                desc="ingest: masked mean-pool + L2 norm, 256 chunks x 512 tok x 1024-d fp32 per step per GPU (configs[4])"),
 }
@@ -389,11 +391,13 @@ def main():
     e2e_val = Q * args.steps / (ms_e2e * 1e-3)
     line = dict(metric="exact cosine top-k queries/sec", value=value, unit="queries/s", n_gpus=world, steps=args.steps,
                 warmup=args.warmup, ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="strong",
-                vs_baseline=None, dtype="bf16" if w["dtype"] == "bf16" and Q > 4 else "f32", data="synthetic",
+                vs_baseline=None, dtype=("bf16" if w["dtype"] == "bf16" else "tf32") if Q > 4 else "f32", data="synthetic",
                 config={"workload": args.workload, "desc": w["desc"], "rows": N, "rows_per_gpu": n_local, "dim": D,
                         "store_dtype": w["dtype"], "Q": Q, "k": k, "path": args.path, "exchange": exchange,
                         "arithmetic": ("bf16 x bf16 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
-                                       if w["dtype"] == "bf16" and Q > 4 else "fp32 FMA dot products"),
+                                       if w["dtype"] == "bf16" and Q > 4 else
+                                       "tf32 x tf32 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
+                                       if Q > 4 else "fp32 FMA dot products"),
                         "l2": "inputs larger than L2: every step streams the whole shard "
                               f"({n_local * D * elem / 1e9:.2f} GB >> 126 MB L2)"},
                 e2e=dict(value=e2e_val, unit="queries/s", h2d_bytes_per_step=Q * D * 4, d2h_bytes_per_step=Q * k * 12,

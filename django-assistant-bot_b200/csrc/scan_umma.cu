@@ -33,7 +33,9 @@ constexpr int kSmemBudget = 227 * 1024 - 2048;  // keep room for alignment slack
 __global__ void __launch_bounds__(kThreads, 1)
 scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
                  const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pad, int stages,
-                 int tmem_cols, int groups, const __grid_constant__ LevelPlan plan) {
+                 int tmem_cols, int groups, int f32, const __grid_constant__ LevelPlan plan) {
+    // f32 != 0: fp32 store and fp32 queries, scored with kind::tf32 (K = 8 per MMA); a k-block is
+    // 128 bytes of a row either way: 64 bf16 or 32 fp32
     extern __shared__ unsigned char smem_raw[];
     const int lvl = sc.ctrl->cur_level;
     if (lvl >= plan.num_levels) return;
@@ -50,8 +52,9 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     const int nq = max(0, min(n_pad, nq_all - slice * n_pad));
 
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int num_kb = sv.dim / kBlockK;
-    const int b_kb_bytes = n_pad * kBlockK * 2;           // one k-block of the query operand
+    const int kb_elems = f32 ? kBlockK / 2 : kBlockK;     // elements per 128-byte k-block
+    const int num_kb = sv.dim / kb_elems;
+    const int b_kb_bytes = n_pad * 128;                   // one k-block of the query operand
     unsigned char *b_smem = smem;                          // [num_kb][n_pad rows x 128 B]
     unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;  // [stages][128 rows x 128 B]
     float *tau_s = reinterpret_cast<float *>(a_smem + (size_t)stages * kAStageBytes);  // [256]
@@ -93,7 +96,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
         if (lane == 0) {
             mbar_arrive_expect_tx(b_full, (uint32_t)(num_kb * b_kb_bytes));
             for (int kb = 0; kb < num_kb; kb++)
-                tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kBlockK, slice * n_pad, b_full);
+                tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kb_elems, slice * n_pad, b_full);
             int s = 0;
             uint32_t ph = 0;
             for (long long it = 0; it < my_tiles; it++) {
@@ -102,7 +105,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
                 for (int kb = 0; kb < num_kb; kb++) {
                     mbar_wait_bounded(&empty[s], ph ^ 1u);
                     mbar_arrive_expect_tx(&full[s], kAStageBytes);
-                    tma_load_2d(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s]);
+                    tma_load_2d(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s]);
                     if (++s == stages) { s = 0; ph ^= 1u; }
                 }
             }
@@ -110,7 +113,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
         if (lane == 0) {
-            const uint32_t idesc = make_idesc(n_pad);
+            const uint32_t idesc = f32 ? make_idesc_tf32(n_pad) : make_idesc(n_pad);
             mbar_wait_bounded(b_full, 0);
             tc_fence_after();
             int s = 0;
@@ -128,8 +131,11 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
                     const uint64_t db = make_smem_desc(smem_u32(b_smem + (size_t)kb * b_kb_bytes));
 #pragma unroll
                     for (int k = 0; k < kBlockK / kUmmaK; k++) {
-                        // advancing K by 16 elements = 32 bytes inside the swizzle atom: +2 in the address field
-                        umma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                        // advancing K by one MMA (16 bf16 or 8 fp32) = 32 bytes inside the swizzle atom: +2 in the address field
+                        if (f32)
+                            umma_tf32(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                        else
+                            umma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty[s]);                    // smem stage reusable once these MMAs finish
                     if (++s == stages) { s = 0; ph ^= 1u; }
@@ -176,9 +182,9 @@ struct UmmaPlan {
     size_t smem;
 };
 
-bool plan_umma(int dim, int nq, UmmaPlan *out) {
+bool plan_umma(int dim, int nq, int elem_bytes, UmmaPlan *out) {
     const int n_pad = nq <= 16 ? 16 : (nq + 15) / 16 * 16;
-    const size_t b_bytes = (size_t)n_pad * dim * 2;
+    const size_t b_bytes = (size_t)n_pad * dim * elem_bytes;
     const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 8) * sizeof(uint64_t) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
     int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
@@ -193,21 +199,25 @@ bool plan_umma(int dim, int nq, UmmaPlan *out) {
     return true;
 }
 
+int elem_bytes_of(int dtype) { return dtype == DAB_BF16 ? 2 : 4; }
+
 }  // namespace
 
 int umma_tile_rows() { return kTileRows; }
 
+// bf16 stores (kind::f16) and fp32 stores (kind::tf32); a row must be a whole number of 128-byte k-blocks
 bool umma_supported(int dim, int dtype) {
     UmmaPlan p;
-    return dtype == DAB_BF16 && dim % kBlockK == 0 && plan_umma(dim, 16, &p);
+    if (dtype != DAB_BF16 && dtype != DAB_F32) return false;
+    return (dim * elem_bytes_of(dtype)) % 128 == 0 && plan_umma(dim, 16, elem_bytes_of(dtype), &p);
 }
 
-// the widest query block whose bf16 copy stays resident in shared memory next to >= 4 corpus stages
-int umma_queries_per_pass(int dim) {
+// the widest query block whose copy stays resident in shared memory next to >= 4 corpus stages
+int umma_queries_per_pass(int dim, int dtype) {
     int best = 0;
     UmmaPlan p;
     for (int n = 16; n <= DAB_MAX_QUERY_BATCH; n += 16)
-        if (plan_umma(dim, n, &p)) best = n;
+        if (plan_umma(dim, n, elem_bytes_of(dtype), &p)) best = n;
     return best;
 }
 
@@ -215,30 +225,34 @@ void umma_release_maps(void *) {}
 
 int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq, const LevelPlan &plan,
                      int num_sms, cudaStream_t st) {
-    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK) return fail(DAB_E_INVALID, "scan_umma: needs a bf16 store with dim % 64 == 0");
+    if (!umma_supported(sv.dim, sv.dtype))
+        return fail(DAB_E_INVALID, "scan_umma: needs a bf16 (dim % 64 == 0) or fp32 (dim % 32 == 0) store");
     if (plan.tile_rows != kTileRows) return fail(DAB_E_INVALID, "scan_umma: level plan built for another tile size");
+    const bool f32 = sv.dtype == DAB_F32;
+    const int eb = elem_bytes_of(sv.dtype);
     // one slice if the whole query block stays resident in shared memory, else `groups` equal slices
-    const int qpass = umma_queries_per_pass(sv.dim);
+    const int qpass = umma_queries_per_pass(sv.dim, sv.dtype);
     if (qpass <= 0 || nq < 1) return fail(DAB_E_INVALID, "scan_umma: query block does not fit shared memory");
     const int groups = (nq + qpass - 1) / qpass;
     const int per_slice = (nq + groups - 1) / groups;
+    // B comes from the unit-norm fp32 queries (fp32 stores) or from their bf16 copy (bf16 stores); rows past
+    // the live queries hold stale data whose columns the epilogue ignores, rows past the buffer read as zero
+    const int q_rows = (f32 ? DAB_MAX_QUERY_BATCH : 2 * DAB_MAX_QUERY_BATCH) - q0;
     UmmaPlan up;
-    if (!plan_umma(sv.dim, per_slice, &up) || groups * up.n_pad > 2 * DAB_MAX_QUERY_BATCH - q0 || groups > num_sms)
+    if (!plan_umma(sv.dim, per_slice, eb, &up) || groups > num_sms)
         return fail(DAB_E_INVALID, "scan_umma: query block does not fit shared memory");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
-    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows)) return rc;
-    // B = rows q0 .. of the bf16 query copy, n_pad rows per slice; rows past the live queries hold stale
-    // data whose columns the epilogue ignores.  The buffer is 2*DAB_MAX_QUERY_BATCH rows long.
-    if (int rc = make_map(&tmap_q, sc.qsplit + (size_t)q0 * sv.dim, (uint64_t)(2 * DAB_MAX_QUERY_BATCH - q0), (uint64_t)sv.dim,
-                          (uint32_t)up.n_pad))
-        return rc;
+    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
+    const void *qbase = f32 ? static_cast<const void *>(sc.qhat + (size_t)q0 * sv.dim)
+                            : static_cast<const void *>(sc.qsplit + (size_t)q0 * sv.dim);
+    if (int rc = make_map(&tmap_q, qbase, (uint64_t)q_rows, (uint64_t)sv.dim, (uint32_t)up.n_pad, f32)) return rc;
     DAB_CUDA_OK(cudaFuncSetAttribute(scan_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)up.smem));
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long seqs = max_tiles < num_sms / groups ? max_tiles : num_sms / groups;
     const int grid = (int)seqs * groups;
     scan_umma_kernel<<<grid, kThreads, up.smem, st>>>(tmap_rows, tmap_q, sv, allow, sc, q0, nq, up.n_pad, up.stages, up.tmem_cols,
-                                                      groups, plan);
+                                                      groups, f32 ? 1 : 0, plan);
     DAB_LAUNCH_OK();
     return DAB_OK;
 }

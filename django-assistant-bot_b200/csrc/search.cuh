@@ -55,7 +55,7 @@ int launch_scan_simt(const StoreView &sv, const uint32_t *allow, const SearchScr
 
 int umma_tile_rows();
 bool umma_supported(int dim, int dtype);
-int umma_queries_per_pass(int dim);
+int umma_queries_per_pass(int dim, int dtype = DAB_BF16);
 int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
                      const LevelPlan &plan, int num_sms, cudaStream_t st);
 

@@ -65,6 +65,9 @@ struct dab_store {
     void *io_host = nullptr;
     void *io_dev = nullptr;
     std::mutex io_mu;  // one host-buffer search at a time per store (they share the staging buffers)
+    // Searches on one store share its scratch: the mutex orders their ENQUEUE, this event orders their
+    // EXECUTION when callers use different streams (each search waits for the previous one's last kernel).
+    cudaEvent_t scratch_free = nullptr;
     std::mutex mu;
 };
 
@@ -197,6 +200,7 @@ extern "C" DAB_API void dab_store_destroy(dab_store *s) {
     cudaFree(s->ids);
     cudaFree(s->scratch_base);
     if (s->status_host) cudaFreeHost(s->status_host);
+    if (s->scratch_free) cudaEventDestroy(s->scratch_free);
     if (s->io_host) cudaFreeHost(s->io_host);
     cudaFree(s->io_dev);
     delete s;
@@ -234,7 +238,7 @@ extern "C" DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds) {
 extern "C" DAB_API int dab_store_set_path(dab_store *s, int path) {
     if (int rc = check_store(s, "dab_store_set_path")) return rc;
     if (path < 0 || path > 2) return fail(DAB_E_INVALID, "dab_store_set_path: 0 auto, 1 CUDA cores, 2 tcgen05");
-    if (path == 2 && !umma_supported(s->dim, s->dtype)) return fail(DAB_E_INVALID, "dab_store_set_path: tcgen05 path needs a bf16 store with dim % 64 == 0");
+    if (path == 2 && !umma_supported(s->dim, s->dtype)) return fail(DAB_E_INVALID, "dab_store_set_path: tcgen05 path needs a bf16 store with dim % 64 == 0 or an fp32 store with dim % 32 == 0");
     std::lock_guard<std::mutex> g(s->mu);
     s->path = path;
     return DAB_OK;
@@ -313,14 +317,16 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
         // Cauchy-Schwarz |approx - exact| <= 2^-8 for unit vectors, plus fp32 accumulation noise
         // (<= dim * 2^-24).  Everything within twice that bound of the k-th best approximate score
         // can still belong to the exact top-k: it is kept (up to k_cap) and rescored in fp32.
-        const float eps = 0.00390625f + (float)dim * 6e-8f;
+        // (fp32 stores go through kind::tf32: both operands lose their low 13 mantissa bits, |d| < 2^-10 each,
+        // so the product is off by < 2^-9 relative.)
+        const float eps = (dtype == DAB_F32 ? 0.001953125f : 0.00390625f) + (float)dim * 6e-8f;
         sp.margin = 2.0f * eps;
         sp.k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // wide blocks that do not fit one SM's shared memory go to the 4-CTA cluster kernel
         static const bool no_quad = getenv("DAB_NO_QUAD") != nullptr;  // tuning aid: use query-slice groups instead
         // queries-as-A kernel: parity-green but measured slower than the cluster kernel; opt-in
         static const bool use_qa = getenv("DAB_USE_QA") != nullptr;
-        const bool wide = nq > umma_queries_per_pass(dim);
+        const bool wide = nq > umma_queries_per_pass(dim, dtype);
         sp.qa = wide && use_qa && qa_supported(dim, dtype, nq);
         sp.quad = wide && !sp.qa && !no_quad && quad_supported(dim, dtype, nq);
         // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
@@ -342,7 +348,7 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
     const LevelPlan &plan = sp.levels;
     *num_levels_out = plan.num_levels;
     if (sp.path == 2) {
-        if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, true, st, first_chunk)) return rc;
+        if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, sv.dtype == DAB_BF16, st, first_chunk)) return rc;
         for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
             {
                 // one launch scores all nq queries
@@ -410,6 +416,8 @@ extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q,
     sv.n = s->size;
     sv.dim = s->dim;
     sv.dtype = s->dtype;
+    if (!s->scratch_free) DAB_CUDA_OK(cudaEventCreateWithFlags(&s->scratch_free, cudaEventDisableTiming));
+    DAB_CUDA_OK(cudaStreamWaitEvent(st, s->scratch_free, 0));   // no-op for the stream that recorded it last
     ScanTimer whole(s->prof, st, true);
     struct Stop {
         ScanTimer &t;
@@ -423,6 +431,7 @@ extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q,
             return rc;
         s->last_num_levels = levels;
     }
+    DAB_CUDA_OK(cudaEventRecord(s->scratch_free, st));
     return DAB_OK;
 }
 

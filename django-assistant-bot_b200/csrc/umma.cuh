@@ -70,6 +70,19 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t make_idesc(int n, int m = kTileRows) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
+// kind::tf32 descriptor: A=B=tf32 (format code 2); fp32 operands are read with their low 13 mantissa bits dropped
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int n, int m = kTileRows) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+// fp32 operands on the tensor cores: K = 8 elements (32 bytes) per instruction
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 
 // a spin that cannot hang the GPU: a lost arrival traps instead (the host sees a launch failure)
 __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity) {
@@ -233,15 +246,17 @@ inline EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-// 2-D bf16 row-major [rows, dim] tensor, box = [box_rows x 64 columns], 128-byte swizzle, OOB rows read as zero
-inline int make_map(CUtensorMap *map, const void *base, uint64_t rows, uint64_t dim, uint32_t box_rows) {
+// 2-D row-major [rows, dim] tensor (bf16, or fp32 when f32 is set), box = [box_rows x 128 bytes of columns],
+// 128-byte swizzle, OOB rows read as zero
+inline int make_map(CUtensorMap *map, const void *base, uint64_t rows, uint64_t dim, uint32_t box_rows, bool f32 = false) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return fail(DAB_E_CUDA, "cuTensorMapEncodeTiled not available from the driver");
     const cuuint64_t gdim[2] = {dim, rows};
-    const cuuint64_t gstride[1] = {dim * 2};
-    const cuuint32_t box[2] = {(cuuint32_t)kBlockK, box_rows};
+    const cuuint64_t gstride[1] = {dim * (f32 ? 4u : 2u)};
+    const cuuint32_t box[2] = {(cuuint32_t)(f32 ? kBlockK / 2 : kBlockK), box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
+    const CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                          const_cast<void *>(base), gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(DAB_E_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));

@@ -238,7 +238,9 @@ class ChunkStore:
             if allow_bitmap.numel() * 32 < len(self):
                 raise DabError(_lib.DAB_E_INVALID, "allow bitmap shorter than the store")
             aptr = allow_bitmap.data_ptr()
-        with torch.cuda.device(self.device):
+        # one checked search at a time per store: the verdict word read after a search belongs to the
+        # most recent search on this store (the GIL is released inside the C call)
+        with self._lock, torch.cuda.device(self.device):
             check(lib().dab_store_search_host(self._h, q.ctypes.data, Q, int(k), aptr, scores.ctypes.data, ids.ctypes.data,
                                               _stream(self.device)))
         return scores, ids

@@ -86,11 +86,38 @@ def test_auto_path_picks_tensor_cores_for_batches():
     np.testing.assert_allclose(sc_auto, sc_simt, rtol=1e-5, atol=1e-6)
 
 
-def test_tcgen05_rejected_for_fp32_store():
+def test_tcgen05_rejected_when_rows_are_not_whole_k_blocks():
     from dab_b200 import DabError, ops
-    store = ops.ChunkStore(100, 768, torch.float32, DEV)
-    with pytest.raises(DabError, match="bf16 store"):
+    store = ops.ChunkStore(100, 100, torch.float32, DEV)       # 400-byte rows: not a multiple of 128 bytes
+    with pytest.raises(DabError, match="tcgen05 path needs"):
         store.set_path("tcgen05")
+    store.close()
+
+
+@pytest.mark.parametrize("N,D,Q,k", [(50_000, 768, 16, 10), (120_000, 768, 48, 100), (30_000, 384, 33, 5),
+                                     (40_000, 768, 100, 20), (20_000, 1024, 7, 250), (300, 32, 5, 10)])
+def test_tf32_tensor_path_on_fp32_stores(N, D, Q, k):
+    """fp32 stores (what pgvector holds) with more than 4 queries: kind::tf32 MMAs + the same margin
+    + exact fp32 rescoring; the final ranking must meet the exact bar."""
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(N + D + Q + k)
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    rows[N // 3] = 0
+    rows[N // 2] = rows[11]
+    queries[0] = rows[11]
+    store = ops.ChunkStore(N, D, torch.float32, DEV)
+    store.append(rows.to(DEV))
+    assert store.describe_plan(Q, k)["path"] == "tcgen05"        # auto: tensor cores once Q > 4
+    scores, ids = store.search(queries.to(DEV), k)
+    S = search_ref.exact_scores(rows.numpy(), queries.numpy())
+    ids, scores = ids.cpu().numpy(), scores.cpu().numpy()
+    for qi in range(Q):
+        search_ref.check_topk_parity(S[qi], ids[qi], scores[qi], k)
+    assert ids[0, 0] == 11 and ids[0, 1] == N // 2
+    store.set_path("simt")
+    s2, i2 = store.search(queries.to(DEV), k)
+    np.testing.assert_array_equal(i2.cpu().numpy(), ids)
     store.close()
 
 
