@@ -30,11 +30,12 @@ constexpr int kMaxStages = 8;
 constexpr int kMinStages = 4;
 constexpr int kSmemBudget = 227 * 1024 - 2048;  // keep room for alignment slack
 
+template <bool F32>
 __global__ void __launch_bounds__(kThreads, 1)
 scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
                  const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pad, int stages,
-                 int tmem_cols, int groups, int f32, const __grid_constant__ LevelPlan plan) {
-    // f32 != 0: fp32 store and fp32 queries, scored with kind::tf32 (K = 8 per MMA); a k-block is
+                 int tmem_cols, int groups, const __grid_constant__ LevelPlan plan) {
+    // F32: fp32 store and fp32 queries, scored with kind::tf32 (K = 8 per MMA); a k-block is
     // 128 bytes of a row either way: 64 bf16 or 32 fp32
     extern __shared__ unsigned char smem_raw[];
     const int lvl = sc.ctrl->cur_level;
@@ -52,7 +53,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     const int nq = max(0, min(n_pad, nq_all - slice * n_pad));
 
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int kb_elems = f32 ? kBlockK / 2 : kBlockK;     // elements per 128-byte k-block
+    constexpr int kb_elems = F32 ? kBlockK / 2 : kBlockK;    // elements per 128-byte k-block
     const int num_kb = sv.dim / kb_elems;
     const int b_kb_bytes = n_pad * 128;                   // one k-block of the query operand
     unsigned char *b_smem = smem;                          // [num_kb][n_pad rows x 128 B]
@@ -113,7 +114,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
         if (lane == 0) {
-            const uint32_t idesc = f32 ? make_idesc_tf32(n_pad) : make_idesc(n_pad);
+            const uint32_t idesc = F32 ? make_idesc_tf32(n_pad) : make_idesc(n_pad);
             mbar_wait_bounded(b_full, 0);
             tc_fence_after();
             int s = 0;
@@ -132,7 +133,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
 #pragma unroll
                     for (int k = 0; k < kBlockK / kUmmaK; k++) {
                         // advancing K by one MMA (16 bf16 or 8 fp32) = 32 bytes inside the swizzle atom: +2 in the address field
-                        if (f32)
+                        if constexpr (F32)
                             umma_tf32(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
                         else
                             umma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
@@ -246,13 +247,13 @@ int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScr
     const void *qbase = f32 ? static_cast<const void *>(sc.qhat + (size_t)q0 * sv.dim)
                             : static_cast<const void *>(sc.qsplit + (size_t)q0 * sv.dim);
     if (int rc = make_map(&tmap_q, qbase, (uint64_t)q_rows, (uint64_t)sv.dim, (uint32_t)up.n_pad, f32)) return rc;
-    DAB_CUDA_OK(cudaFuncSetAttribute(scan_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)up.smem));
+    auto kernel = f32 ? scan_umma_kernel<true> : scan_umma_kernel<false>;
+    DAB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)up.smem));
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long seqs = max_tiles < num_sms / groups ? max_tiles : num_sms / groups;
     const int grid = (int)seqs * groups;
-    scan_umma_kernel<<<grid, kThreads, up.smem, st>>>(tmap_rows, tmap_q, sv, allow, sc, q0, nq, up.n_pad, up.stages, up.tmem_cols,
-                                                      groups, f32 ? 1 : 0, plan);
+    kernel<<<grid, kThreads, up.smem, st>>>(tmap_rows, tmap_q, sv, allow, sc, q0, nq, up.n_pad, up.stages, up.tmem_cols, groups, plan);
     DAB_LAUNCH_OK();
     return DAB_OK;
 }
