@@ -38,7 +38,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     // F32: fp32 store and fp32 queries, scored with kind::tf32 (K = 8 per MMA); a k-block is
     // 128 bytes of a row either way: 64 bf16 or 32 fp32
     extern __shared__ unsigned char smem_raw[];
-    const int lvl = sc.ctrl->cur_level;
+    const int lvl = (int)warp_uniform((uint32_t)sc.ctrl->cur_level);
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];
     // Query-slice groups: when the query block is too wide to stay resident in one SM's shared
@@ -89,12 +89,12 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_base_s;
+    const uint32_t tmem_base = warp_uniform(*tmem_base_s);
     const long long my_tiles = (ntiles - seq + num_seq - 1) / num_seq;
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        if (elect_one()) {
             mbar_arrive_expect_tx(b_full, (uint32_t)(num_kb * b_kb_bytes));
             for (int kb = 0; kb < num_kb; kb++)
                 tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kb_elems, slice * n_pad, b_full);
@@ -113,7 +113,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t idesc = F32 ? make_idesc_tf32(n_pad) : make_idesc(n_pad);
             mbar_wait_bounded(b_full, 0);
             tc_fence_after();

@@ -67,14 +67,14 @@ __global__ void __launch_bounds__(kThreads, 1)
 scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv, const uint32_t *__restrict__ allow,
                     SearchScratch sc, int q0_all, int nq_all, int stages, const __grid_constant__ LevelPlan plan) {
     extern __shared__ unsigned char smem_raw[];
-    const int lvl = sc.ctrl->cur_level;
+    const int lvl = (int)warp_uniform((uint32_t)sc.ctrl->cur_level);
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];  // steps of 64 rows
     const int pair_id = blockIdx.x / 2;
     const int num_pairs = gridDim.x / 2;
     if ((long long)pair_id >= ntiles) return;           // same decision in both CTAs of the pair
 
-    const uint32_t rank = cluster_ctarank();            // 0 = leader
+    const uint32_t rank = warp_uniform(cluster_ctarank());   // 0 = leader
     const bool leader = rank == 0;
     const int num_kb = sv.dim / kBlockK;
     const int stages_per_step = num_kb / kKbPerStage;
@@ -116,12 +116,12 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
     tc_fence_before();
     cluster_sync_all();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_base_s;
+    const uint32_t tmem_base = warp_uniform(*tmem_base_s);
     const uint32_t tmem_acc0 = tmem_base + (uint32_t)a_cols;   // accumulators live after the query columns
     const long long my_steps = (ntiles - pair_id + num_pairs - 1) / num_pairs;
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {
             // ------------------------------------------------------------ TMA producer: my 32 rows of every step
             int s = 0;
             uint32_t ph = 0;
@@ -139,7 +139,7 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && leader) {
+        if (leader && elect_one()) {
             // ------------------------------------------------------------ MMA issuer of the pair
             const uint32_t idesc = make_idesc(kStepRows, 2 * kTileRows);   // N = 64 corpus rows, M = 256 queries
             mbar_wait_bounded(a_ready, 0);

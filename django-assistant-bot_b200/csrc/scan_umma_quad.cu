@@ -33,7 +33,7 @@ namespace {
 
 using namespace umma;
 constexpr int kThreads = 256;
-constexpr int kMaxStages = 8;
+constexpr int kMaxStages = 12;
 constexpr int kMinStages = 3;
 constexpr int kMaxAcc = 4;         // TMEM accumulator stages (512 columns / n_pair, at most 4)
 constexpr int kPendCap = 512;       // staged candidates per accumulator stage per CTA
@@ -44,7 +44,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                       const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pair, int stages,
                       int tmem_cols, int num_pairs, int acc_stages, const __grid_constant__ LevelPlan plan) {
     extern __shared__ unsigned char smem_raw[];
-    const int lvl = sc.ctrl->cur_level;
+    const int lvl = (int)warp_uniform((uint32_t)sc.ctrl->cur_level);
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];  // super-tiles of 256 rows
     const int cluster_size = 2 * num_pairs;             // 4 = two pairs sharing one tile stream; 2 = one pair
@@ -52,7 +52,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     const int num_clusters = gridDim.x / cluster_size;
     if ((long long)cluster_id >= ntiles) return;       // same decision in every CTA of the cluster
 
-    const uint32_t rank = cluster_ctarank();
+    const uint32_t rank = warp_uniform(cluster_ctarank());
     const int pair = (int)(rank >> 1), half = (int)(rank & 1);
     const bool leader = half == 0;
     const int n_half = n_pair / 2;                      // query rows of the B operand this CTA holds
@@ -107,11 +107,11 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     tc_fence_before();
     cluster_sync_all();   // barriers of every CTA are initialised before any remote arrive / multicast
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_base_s;
+    const uint32_t tmem_base = warp_uniform(*tmem_base_s);
     const long long my_tiles = (ntiles - cluster_id + num_clusters - 1) / num_clusters;
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {
             // this CTA's quarter of the query block: rows [pair*n_pair + half*n_half, +n_half) of the bf16 copy
             mbar_arrive_expect_tx(b_full, (uint32_t)(num_kb * b_kb_bytes));
             for (int kb = 0; kb < num_kb; kb++)
@@ -122,11 +122,24 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                 const uint16_t mask = (uint16_t)((1u << rank) | (num_pairs == 2 ? (1u << (rank + 2)) : 0u));
                 int s = 0;
                 uint32_t ph = 0;
+#ifdef DAB_EXP_TIMING
+                long long tm_empty = 0, tm_pstart = clock64();
+#endif
                 for (long long it = 0; it < my_tiles; it++) {
                     const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
                     const int row0 = (int)(t * kSuperRows) + half * kTileRows;
                     for (int kb = 0; kb < num_kb; kb++) {
+#ifdef DAB_EXP_NOLOAD
+                        if (kb >= 0) continue;
+#endif
+#ifdef DAB_EXP_TIMING
+                        long long t2_ = clock64();
+#endif
                         mbar_wait_bounded(&empty[s], ph ^ 1u);
+#ifdef DAB_EXP_TIMING
+                        tm_empty += clock64() - t2_;
+#endif
+
                         if (num_pairs == 2)
                             tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s], mask);
                         else
@@ -134,10 +147,13 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                         if (++s == stages) { s = 0; ph ^= 1u; }
                     }
                 }
+#ifdef DAB_EXP_TIMING
+                if (blockIdx.x == 0) printf("[lvl %d cta 0] producer: total %lld wait_empty %lld\n", lvl, clock64() - tm_pstart, tm_empty);
+#endif
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && leader) {
+        if (leader && elect_one()) {
             // ------------------------------------------------------------ MMA issuer of the pair
             const uint32_t idesc = make_idesc(n_pair, kSuperRows);
             const uint16_t pair_mask = (uint16_t)(0x3u << (2 * pair));
@@ -145,27 +161,59 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             tc_fence_after();
             int s = 0;
             uint32_t ph = 0;
+#ifdef DAB_EXP_TIMING
+            long long tm_tmem = 0, tm_full = 0, tm_start = clock64();
+#endif
             for (long long it = 0; it < my_tiles; it++) {
                 const int a = (int)(it % acc_stages);
                 const uint32_t aph = (uint32_t)((it / acc_stages) & 1);
+#ifdef DAB_EXP_TIMING
+                long long t0_ = clock64();
+#endif
                 mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);
+#ifdef DAB_EXP_TIMING
+                tm_tmem += clock64() - t0_;
+#endif
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(a * n_pair);
                 for (int kb = 0; kb < num_kb; kb++) {
                     // both 16 KiB halves of the stage (mine and my peer's) report to this barrier
+#ifndef DAB_EXP_NOLOAD
                     mbar_arrive_expect_tx(&full[s], 2 * kAStageBytes);
+#endif
+#ifdef DAB_EXP_TIMING
+                    long long t1_ = clock64();
+#endif
+#ifndef DAB_EXP_NOLOAD
                     mbar_wait_bounded(&full[s], ph);
+#endif
+#ifdef DAB_EXP_TIMING
+                    tm_full += clock64() - t1_;
+#endif
+#ifndef DAB_EXP_NOKBFENCE
                     tc_fence_after();
+#endif
                     const uint64_t da = make_smem_desc(smem_u32(a_smem + (size_t)s * kAStageBytes));
                     const uint64_t db = make_smem_desc(smem_u32(b_smem + (size_t)kb * b_kb_bytes));
+#ifndef DAB_EXP_MMAS
+#define DAB_EXP_MMAS (kBlockK / kUmmaK)
+#endif
 #pragma unroll
-                    for (int k = 0; k < kBlockK / kUmmaK; k++)
+                    for (int k = 0; k < DAB_EXP_MMAS; k++)
                         umma_f16_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+#ifdef DAB_EXP_COMMIT_EVERY
+                    if (kb % DAB_EXP_COMMIT_EVERY == DAB_EXP_COMMIT_EVERY - 1)
+#endif
                     umma_commit_mc2(&empty[s], (uint16_t)0x3u);        // the loaders are ranks 0 and 1
                     if (++s == stages) { s = 0; ph ^= 1u; }
                 }
                 umma_commit_mc2(&tmem_full[a], pair_mask);
             }
+#ifdef DAB_EXP_TIMING
+            if (blockIdx.x == 0 || blockIdx.x == 2)
+                printf("[lvl %d cta %d] issuer: tiles %lld total %lld wait_tmem_empty %lld wait_full %lld\n", lvl, (int)blockIdx.x, my_tiles,
+                       clock64() - tm_start, tm_tmem, tm_full);
+#endif
         }
     } else if (warp == 3) {
         if (lane == 0) {
@@ -196,6 +244,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         };
         long long row = row_of(0);
         float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
+#ifdef DAB_EXP_TIMING
+        long long te_pend = 0, te_full = 0, te_start = clock64();
+#endif
         for (long long it = 0; it < my_tiles; it++) {
             const int a = (int)(it % acc_stages);                  // accumulator stage
             const uint32_t aph = (uint32_t)((it / acc_stages) & 1);
@@ -203,12 +254,24 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             const uint32_t plph = (uint32_t)((it >> 1) & 1);
             const long long row_next = it + 1 < my_tiles ? row_of(it + 1) : sv.n;
             const float rinv_next = row_next < sv.n ? sv.inv_norm[row_next] : 0.f;
+#ifdef DAB_EXP_TIMING
+            long long t3_ = clock64();
+#endif
             mbar_wait_bounded(&pend_free[pl], plph ^ 1u);     // the flusher is done with this list (tile it-2)
+#ifdef DAB_EXP_TIMING
+            long long t4_ = clock64();
+            te_pend += t4_ - t3_;
+#endif
             mbar_wait_bounded(&tmem_full[a], aph);
+#ifdef DAB_EXP_TIMING
+            te_full += clock64() - t4_;
+#endif
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair);
             const PendList pend = {pend_key + pl * kPendCap, pend_q + pl * kPendCap, pend_n + pl, kPendCap};
+#ifndef DAB_EXP_NOEPI
             epilogue_tile(taddr, (nq + 15) & ~15, rinv, row, tau_s, q0, allow, sc, &pend);
+#endif
             row = row_next;
             rinv = rinv_next;
             tc_fence_before();
@@ -218,6 +281,11 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                 mbar_arrive(&pend_full[pl]);
             }
         }
+#ifdef DAB_EXP_TIMING
+        if (blockIdx.x < 2 && lane == 0 && warp == 4)
+            printf("[lvl %d cta %d] epilogue w4: total %lld wait_pend_free %lld wait_tmem_full %lld\n", lvl, (int)blockIdx.x,
+                   clock64() - te_start, te_pend, te_full);
+#endif
     }
     // ---------------------------------------------------------------- teardown
     tc_fence_before();
@@ -306,6 +374,7 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     int acc = qp.tmem_cols / qp.n_pair;
     if (acc > kMaxAcc) acc = kMaxAcc;
     if (const char *e = getenv("DAB_QUAD_ACC")) acc = atoi(e) >= 2 && atoi(e) <= acc ? atoi(e) : acc;  // tuning aid
+    if (const char *e = getenv("DAB_QUAD_STAGES")) qp.stages = atoi(e) >= 2 && atoi(e) <= qp.stages ? atoi(e) : qp.stages;
     static const bool debug = getenv("DAB_DEBUG") != nullptr;
     if (debug)
         fprintf(stderr, "[dab] quad: pairs=%d nq=%d n_pair=%d stages=%d tmem_cols=%d smem=%zu max_clusters=%d clusters=%lld levels=%d\n", num_pairs, nq,
