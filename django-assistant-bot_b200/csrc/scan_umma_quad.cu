@@ -32,7 +32,7 @@ namespace dab {
 namespace {
 
 using namespace umma;
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;         // warps 0-3: roles; warps 4-11: epilogue (two per TMEM lane quarter)
 constexpr int kMaxStages = 12;
 constexpr int kMinStages = 3;
 constexpr int kMaxAcc = 4;         // TMEM accumulator stages (512 columns / n_pair, at most 4)
@@ -88,10 +88,10 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         mbar_init(b_pair, 2);
         for (int a = 0; a < kMaxAcc; a++) {
             mbar_init(&tmem_full[a], 1);
-            mbar_init(&tmem_empty[a], 8);
+            mbar_init(&tmem_empty[a], 16);   // 8 epilogue warps x 2 CTAs
         }
         for (int a = 0; a < 2; a++) {
-            mbar_init(&pend_full[a], 4);
+            mbar_init(&pend_full[a], 8);
             mbar_init(&pend_free[a], 1);
             pend_n[a] = 0;
         }
@@ -236,7 +236,13 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------------ epilogue (own TMEM half)
-        const int wq = warp & 3;
+        const int wq = warp & 3;                               // TMEM lane quarter this warp may read
+        // two warps share a lane quarter and split the pair's query columns (whole 16-column slabs each):
+        // one warp per quarter was the critical path once the MMAs ran at their floor
+        const int ncols = (nq + 15) & ~15;
+        const int c_split = (ncols / 16 + 1) / 2 * 16;
+        const int c_begin = warp >= 8 ? c_split : 0;
+        const int c_count = warp >= 8 ? ncols - c_split : c_split;
         // the row's 1/|row| for the NEXT tile is fetched while the current one is drained
         auto row_of = [&](long long it_) {
             const long long t = level_tile(plan, lvl, cluster_id + it_ * num_clusters);
@@ -267,10 +273,10 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             te_full += clock64() - t4_;
 #endif
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair);
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair + c_begin);
             const PendList pend = {pend_key + pl * kPendCap, pend_q + pl * kPendCap, pend_n + pl, kPendCap};
 #ifndef DAB_EXP_NOEPI
-            epilogue_tile(taddr, (nq + 15) & ~15, rinv, row, tau_s, q0, allow, sc, &pend);
+            epilogue_tile(taddr, c_count, rinv, row, tau_s + c_begin, q0 + c_begin, allow, sc, &pend);
 #endif
             row = row_next;
             rinv = rinv_next;
