@@ -129,6 +129,9 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 const long long t = level_tile(plan, lvl, pair_id + it * num_pairs);
                 const int row0 = (int)(t * kStepRows) + (int)rank * kHalfRows;
                 for (int st = 0; st < stages_per_step; st++) {
+#ifdef DAB_EXP_NOLOAD
+                    if (st >= 0) continue;
+#endif
                     mbar_wait_bounded(&empty[s], ph ^ 1u);
                     unsigned char *dst = b_smem + (size_t)s * kStageBytes;
 #pragma unroll
@@ -146,15 +149,32 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             tc_fence_after();
             int s = 0;
             uint32_t ph = 0;
+#ifdef DAB_EXP_TIMING
+            long long tm_tmem = 0, tm_full = 0, tm_start = clock64();
+#endif
             for (long long it = 0; it < my_steps; it++) {
                 const int a = (int)(it & 1);
                 const uint32_t aph = (uint32_t)((it >> 1) & 1);
+#ifdef DAB_EXP_TIMING
+                long long t0_ = clock64();
+#endif
                 mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);
+#ifdef DAB_EXP_TIMING
+                tm_tmem += clock64() - t0_;
+#endif
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_acc0 + (uint32_t)(a * kAccCols);
                 for (int st = 0; st < stages_per_step; st++) {
+#ifndef DAB_EXP_NOLOAD
                     mbar_arrive_expect_tx(&full[s], 2 * kStageBytes);      // my half + my peer's half
+#ifdef DAB_EXP_TIMING
+                    long long t1_ = clock64();
+#endif
                     mbar_wait_bounded(&full[s], ph);
+#ifdef DAB_EXP_TIMING
+                    tm_full += clock64() - t1_;
+#endif
+#endif
                     tc_fence_after();
                     const uint32_t sbase = smem_u32(b_smem + (size_t)s * kStageBytes);
 #pragma unroll
@@ -173,6 +193,10 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 }
                 umma_commit_mc2(&tmem_full[a], (uint16_t)0x3u);
             }
+#ifdef DAB_EXP_TIMING
+            if (blockIdx.x == 0)
+                printf("[lvl %d] qa issuer: steps %lld total %lld wait_tmem_empty %lld wait_full %lld\n", lvl, my_steps, clock64() - tm_start, tm_tmem, tm_full);
+#endif
         }
     } else if (warp == 3) {
         // ------------------------------------------------------------ flusher: staged candidates -> global buffers
@@ -222,6 +246,9 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             const long long r = step_row0(0) + et;
             s_inv[et] = r < sv.n ? sv.inv_norm[r] : 0.f;
         }
+#ifdef DAB_EXP_TIMING
+        long long te_pend = 0, te_full = 0, te_start = clock64();
+#endif
         for (long long it = 0; it < my_steps; it++) {
             const int a = (int)(it & 1);
             const uint32_t aph = (uint32_t)((it >> 1) & 1);
@@ -231,13 +258,24 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 const long long r = step_row0(it + 1) + et;
                 inv_next = r < sv.n ? sv.inv_norm[r] : 0.f;
             }
+#ifdef DAB_EXP_TIMING
+            long long t3_ = clock64();
+#endif
             named_bar_sync(1, 128);                             // s_inv[a] written by all epilogue threads
             mbar_wait_bounded(&pend_free[a], aph ^ 1u);
+#ifdef DAB_EXP_TIMING
+            long long t4_ = clock64();
+            te_pend += t4_ - t3_;
+#endif
             mbar_wait_bounded(&tmem_full[a], aph);
+#ifdef DAB_EXP_TIMING
+            te_full += clock64() - t4_;
+#endif
             tc_fence_after();
             const uint32_t taddr = tmem_acc0 + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * kAccCols);
             const float *inv = s_inv + a * kStepRows;
             uint32_t v0[16], v1[16];
+#ifndef DAB_EXP_NOEPI
             tmem_ld16(taddr, v0);
 #pragma unroll
             for (int c0 = 0; c0 < kStepRows; c0 += 32) {
@@ -260,7 +298,11 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                         pass |= (__uint_as_float(v[j + 2]) * iv.z >= tau ? 1u : 0u) << (j + 2);
                         pass |= (__uint_as_float(v[j + 3]) * iv.w >= tau ? 1u : 0u) << (j + 3);
                     }
+#ifdef DAB_EXP_NOSLOW
+                    if (pass == 0x12345u) {
+#else
                     if (pass) {
+#endif
 #pragma unroll
                         for (int j = 0; j < 16; j++) {
                             if ((pass & (1u << j)) && inv[cb + j] > 0.f) {
@@ -277,6 +319,7 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                     }
                 }
             }
+#endif
             tc_fence_before();
             if (et < kStepRows) s_inv[(a ^ 1) * kStepRows + et] = inv_next;   // for the next step (other stage)
             __syncwarp();
@@ -285,6 +328,10 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 mbar_arrive(&pend_full[a]);
             }
         }
+#ifdef DAB_EXP_TIMING
+        if (blockIdx.x == 0 && tid == 128)
+            printf("[lvl %d] qa epilogue w4: total %lld wait_bar+pend_free %lld wait_tmem_full %lld\n", lvl, clock64() - te_start, te_pend, te_full);
+#endif
     }
     // ---------------------------------------------------------------- teardown
     tc_fence_before();

@@ -36,7 +36,9 @@ constexpr int kThreads = 384;         // warps 0-3: roles; warps 4-11: epilogue 
 constexpr int kMaxStages = 12;
 constexpr int kMinStages = 3;
 constexpr int kMaxAcc = 4;         // TMEM accumulator stages (512 columns / n_pair, at most 4)
-constexpr int kPendCap = 512;       // staged candidates per accumulator stage per CTA
+constexpr int kEpiWarps = 8;
+constexpr int kWarpCap = 64;        // staged candidates per epilogue warp per tile (more go straight to the candidate buffer)
+constexpr int kPendCap = kEpiWarps * kWarpCap;
 constexpr int kSuperRows = 2 * kTileRows;  // corpus rows per MMA pair step (UMMA M = 256)
 constexpr int kSmemBudget = 227 * 1024 - 2048;
 __global__ void __launch_bounds__(kThreads, 1)
@@ -75,8 +77,8 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     uint64_t *pend_free = pend_full + 2;               // [2] the flusher drained list a
     uint64_t *pend_key = pend_free + 2;                // [2][kPendCap]
     uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(pend_key + 2 * kPendCap);
-    uint32_t *pend_n = tmem_base_s + 1;                // [2]
-    uint32_t *pend_q = pend_n + 2;                     // [2][kPendCap]
+    uint32_t *pend_n = tmem_base_s + 1;                // [2][kEpiWarps] hits of each epilogue warp in the tile
+    uint32_t *pend_q = pend_n + 2 * kEpiWarps;         // [2][kPendCap]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -93,7 +95,6 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         for (int a = 0; a < 2; a++) {
             mbar_init(&pend_full[a], 8);
             mbar_init(&pend_free[a], 1);
-            pend_n[a] = 0;
         }
         fence_barrier_init();
         prefetch_tmap(&tmap_rows);
@@ -225,14 +226,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             const int a = (int)(it & 1);
             const uint32_t aph = (uint32_t)((it >> 1) & 1);
             mbar_wait_bounded(&pend_full[a], aph);
-            const uint32_t n = min(pend_n[a], (uint32_t)kPendCap);
-            for (uint32_t i = lane; i < n; i += 32)
-                append_candidate(sc, allow, (int)pend_q[a * kPendCap + i], pend_key[a * kPendCap + i]);
+            flush_warp_lists(pend_key + a * kPendCap, pend_q + a * kPendCap, pend_n + a * kEpiWarps, kEpiWarps, kWarpCap, allow, sc);
             __syncwarp();
-            if (lane == 0) {
-                pend_n[a] = 0;
-                mbar_arrive(&pend_free[a]);
-            }
+            if (lane == 0) mbar_arrive(&pend_free[a]);
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------------ epilogue (own TMEM half)
@@ -274,9 +270,11 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
 #endif
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair + c_begin);
-            const PendList pend = {pend_key + pl * kPendCap, pend_q + pl * kPendCap, pend_n + pl, kPendCap};
+            const int ew = warp - 4;                                // 0..7
+            const WarpList wl = {pend_key + pl * kPendCap + ew * kWarpCap, pend_q + pl * kPendCap + ew * kWarpCap, kWarpCap};
+            uint32_t hits = 0;
 #ifndef DAB_EXP_NOEPI
-            epilogue_tile(taddr, c_count, rinv, row, tau_s + c_begin, q0 + c_begin, allow, sc, &pend);
+            hits = epilogue_tile_wl(taddr, c_count, rinv, row, tau_s + c_begin, q0 + c_begin, allow, sc, wl);
 #endif
             row = row_next;
             rinv = rinv_next;
@@ -284,7 +282,8 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             __syncwarp();
             if (lane == 0) {
                 if (leader) mbar_arrive(&tmem_empty[a]); else mbar_arrive_remote(&tmem_empty[a], rank & ~1u);
-                mbar_arrive(&pend_full[pl]);
+                pend_n[pl * kEpiWarps + ew] = hits;
+                mbar_arrive(&pend_full[pl]);                        // release: the flusher sees the list and its count
             }
         }
 #ifdef DAB_EXP_TIMING
@@ -312,7 +311,7 @@ bool plan_quad(int dim, int nq, int num_pairs, QuadPlan *out) {
     if (n_pair < 32) n_pair = 32;
     if (n_pair > 128) return false;
     const size_t b_bytes = (size_t)(n_pair / 2) * dim * 2;
-    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 +
+    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 + 2 * kEpiWarps * sizeof(uint32_t) +
                          2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
     int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);

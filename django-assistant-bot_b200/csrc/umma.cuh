@@ -181,6 +181,111 @@ __device__ __forceinline__ void epilogue_tile(uint32_t taddr, int ncols, float r
     }
 }
 
+// ---- staging without atomics -------------------------------------------------------------------
+// The admitted-candidate path above costs a shared-memory atomic (and a 16-way divergent branch ladder)
+// per hit; at ~1 hit per 1000 scores that was most of the epilogue's time once the MMAs ran at their
+// floor.  Here every epilogue warp owns a list: the slot of a hit is the warp's running count (a
+// warp-uniform register) plus the number of hitting lanes below it (one ballot) - no atomics, no
+// divergent ladder; the loop below runs once per "some lane still has a hit", all lanes converged.
+struct WarpList {
+    uint64_t *key;   // [cap]
+    uint32_t *q;     // [cap]
+    int cap;
+};
+
+__device__ __forceinline__ uint32_t pick16(const uint32_t (&v)[16], int j) {
+    uint32_t x = v[0];
+#pragma unroll
+    for (int i = 1; i < 16; i++) x = j == i ? v[i] : x;
+    return x;
+}
+
+// 16-column slab of an accumulator row (lane = corpus row, column = query).  Returns the new count.
+__device__ __forceinline__ uint32_t epilogue_slab_wl(const uint32_t (&v)[16], int c0, float rinv, long long row,
+                                                     const float *tau_s, int q_base, const uint32_t *__restrict__ allow,
+                                                     const SearchScratch &sc, const WarpList &wl, uint32_t cnt) {
+    uint32_t pass = 0;
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+        const float4 tq = *reinterpret_cast<const float4 *>(tau_s + c0 + j);
+        pass |= (__uint_as_float(v[j + 0]) * rinv >= tq.x ? 1u : 0u) << (j + 0);
+        pass |= (__uint_as_float(v[j + 1]) * rinv >= tq.y ? 1u : 0u) << (j + 1);
+        pass |= (__uint_as_float(v[j + 2]) * rinv >= tq.z ? 1u : 0u) << (j + 2);
+        pass |= (__uint_as_float(v[j + 3]) * rinv >= tq.w ? 1u : 0u) << (j + 3);
+    }
+    if (!(rinv > 0.f)) pass = 0;   // zero rows and rows past the end never rank
+    const uint32_t lt = (1u << (threadIdx.x & 31)) - 1u;
+    while (__any_sync(0xffffffffu, pass != 0)) {
+        const bool has = pass != 0;
+        const uint32_t b = __ballot_sync(0xffffffffu, has);
+        if (has) {
+            const int j = __ffs(pass) - 1;
+            pass &= pass - 1;
+            const uint64_t key = make_key(__uint_as_float(pick16(v, j)) * rinv, (uint32_t)row);
+            const uint32_t slot = cnt + __popc(b & lt);
+            if (slot < (uint32_t)wl.cap) {
+                wl.key[slot] = key;
+                wl.q[slot] = (uint32_t)(q_base + c0 + j);
+            } else {
+                append_candidate(sc, allow, q_base + c0 + j, key);   // list full (level 0, dense clusters)
+            }
+        }
+        cnt += __popc(b);
+    }
+    return cnt;
+}
+
+// whole accumulator row over `ncols` columns (multiple of 16, warp-uniform); returns the warp's hit count
+__device__ __forceinline__ uint32_t epilogue_tile_wl(uint32_t taddr, int ncols, float rinv, long long row, const float *tau_s,
+                                                     int q_base, const uint32_t *__restrict__ allow, const SearchScratch &sc,
+                                                     const WarpList &wl) {
+    uint32_t cnt = 0;
+    if (ncols <= 0) return cnt;
+    uint32_t v0[16], v1[16];
+    tmem_ld16(taddr, v0);
+    for (int c0 = 0; c0 < ncols; c0 += 32) {
+        tmem_ld_wait();
+        const bool second = c0 + 16 < ncols;
+        if (second) tmem_ld16(taddr + (uint32_t)(c0 + 16), v1);
+        cnt = epilogue_slab_wl(v0, c0, rinv, row, tau_s, q_base, allow, sc, wl, cnt);
+        if (second) {
+            tmem_ld_wait();
+            if (c0 + 32 < ncols) tmem_ld16(taddr + (uint32_t)(c0 + 32), v0);
+            cnt = epilogue_slab_wl(v1, c0 + 16, rinv, row, tau_s, q_base, allow, sc, wl, cnt);
+        }
+    }
+    return cnt;
+}
+
+// The flusher warp's side: `nlists` (<= 8) lists of `cap` entries laid out back to back, counts in cnt_s.
+// One flattened pass, so a tile's candidates cost one global round trip, not one per list.
+__device__ __forceinline__ void flush_warp_lists(const uint64_t *key, const uint32_t *q, const uint32_t *cnt_s, int nlists, int cap,
+                                                 const uint32_t *__restrict__ allow, const SearchScratch &sc) {
+    const int lane = threadIdx.x & 31;
+    uint32_t incl = lane < nlists ? min(cnt_s[lane], (uint32_t)cap) : 0u;
+#pragma unroll
+    for (int d = 1; d < 8; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    uint32_t end[8];
+#pragma unroll
+    for (int w = 0; w < 8; w++) end[w] = __shfl_sync(0xffffffffu, incl, w);
+    const uint32_t total = end[7];
+    for (uint32_t i = lane; i < total; i += 32) {
+        int w = 0;
+        uint32_t begin = 0;
+#pragma unroll
+        for (int ww = 0; ww < 7; ww++)
+            if (i >= end[ww]) {
+                w = ww + 1;
+                begin = end[ww];
+            }
+        const uint32_t e = (uint32_t)(w * cap) + (i - begin);
+        append_candidate(sc, allow, (int)q[e], key[e]);
+    }
+}
+
 // ---- 2-CTA (cta_group::2) and cluster helpers ------------------------------------------------
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the pair bit of a shared::cluster address -> even CTA of the pair
 
