@@ -36,7 +36,9 @@ constexpr int kKbPerStage = 2;                // k-blocks (64 dims each) per sha
 constexpr int kSubBytes = kHalfRows * kBlockK * 2;          // 4 KiB: 32 rows x 128 B
 constexpr int kStageBytes = kKbPerStage * kSubBytes;        // 8 KiB per CTA per stage
 constexpr int kMaxStages = 20;
-constexpr int kPendCap = 512;
+constexpr int kEpiWarps = 4;
+constexpr int kWarpCap = 128;                 // staged candidates per epilogue warp per step
+constexpr int kPendCap = kEpiWarps * kWarpCap;
 constexpr int kAccCols = kStepRows;           // fp32 accumulator columns per stage
 constexpr int kSmemBudget = 227 * 1024 - 2048;
 
@@ -92,8 +94,8 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
     uint64_t *pend_free = pend_full + 2;               // [2]
     uint64_t *pend_key = pend_free + 2;                // [2][kPendCap]
     uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(pend_key + 2 * kPendCap);
-    uint32_t *pend_n = tmem_base_s + 1;                // [2]
-    uint32_t *pend_q = pend_n + 2;                     // [2][kPendCap]
+    uint32_t *pend_n = tmem_base_s + 1;                // [2][kEpiWarps]
+    uint32_t *pend_q = pend_n + 2 * kEpiWarps;         // [2][kPendCap]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -107,7 +109,6 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             mbar_init(&tmem_empty[a], 8);
             mbar_init(&pend_full[a], 4);
             mbar_init(&pend_free[a], 1);
-            pend_n[a] = 0;
         }
         fence_barrier_init();
         prefetch_tmap(&tmap_rows);
@@ -204,14 +205,9 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             const int pl = (int)(it & 1);
             const uint32_t plph = (uint32_t)((it >> 1) & 1);
             mbar_wait_bounded(&pend_full[pl], plph);
-            const uint32_t n = min(pend_n[pl], (uint32_t)kPendCap);
-            for (uint32_t i = lane; i < n; i += 32)
-                append_candidate(sc, allow, (int)pend_q[pl * kPendCap + i], pend_key[pl * kPendCap + i]);
+            flush_warp_lists(pend_key + pl * kPendCap, pend_q + pl * kPendCap, pend_n + pl * kEpiWarps, kEpiWarps, kWarpCap, allow, sc);
             __syncwarp();
-            if (lane == 0) {
-                pend_n[pl] = 0;
-                mbar_arrive(&pend_free[pl]);
-            }
+            if (lane == 0) mbar_arrive(&pend_free[pl]);
         }
     } else if (warp >= 4) {
         const int wq = warp & 3;                               // TMEM lane quarter this warp may touch
@@ -244,7 +240,8 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
         auto step_row0 = [&](long long it_) { return level_tile(plan, lvl, pair_id + it_ * num_pairs) * kStepRows; };
         if (et < kStepRows) {   // inverse norms of the first step
             const long long r = step_row0(0) + et;
-            s_inv[et] = r < sv.n ? sv.inv_norm[r] : 0.f;
+            const float x = r < sv.n ? sv.inv_norm[r] : 0.f;
+            s_inv[et] = x > 0.f ? x : __int_as_float(0x7fc00000);   // zero rows / rows past the end: NaN, never >= tau
         }
 #ifdef DAB_EXP_TIMING
         long long te_pend = 0, te_full = 0, te_start = clock64();
@@ -256,7 +253,8 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             float inv_next = 0.f;
             if (et < kStepRows && it + 1 < my_steps) {          // fetched now, stored after this step is drained
                 const long long r = step_row0(it + 1) + et;
-                inv_next = r < sv.n ? sv.inv_norm[r] : 0.f;
+                const float x = r < sv.n ? sv.inv_norm[r] : 0.f;
+                inv_next = x > 0.f ? x : __int_as_float(0x7fc00000);
             }
 #ifdef DAB_EXP_TIMING
             long long t3_ = clock64();
@@ -275,6 +273,10 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             const uint32_t taddr = tmem_acc0 + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * kAccCols);
             const float *inv = s_inv + a * kStepRows;
             uint32_t v0[16], v1[16];
+            uint32_t hits = 0;
+            const uint32_t lt = (1u << lane) - 1u;
+            uint64_t *wkey = pend_key + a * kPendCap + wq * kWarpCap;
+            uint32_t *wq_ = pend_q + a * kPendCap + wq * kWarpCap;
 #ifndef DAB_EXP_NOEPI
             tmem_ld16(taddr, v0);
 #pragma unroll
@@ -298,24 +300,23 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                         pass |= (__uint_as_float(v[j + 2]) * iv.z >= tau ? 1u : 0u) << (j + 2);
                         pass |= (__uint_as_float(v[j + 3]) * iv.w >= tau ? 1u : 0u) << (j + 3);
                     }
-#ifdef DAB_EXP_NOSLOW
-                    if (pass == 0x12345u) {
-#else
-                    if (pass) {
-#endif
-#pragma unroll
-                        for (int j = 0; j < 16; j++) {
-                            if ((pass & (1u << j)) && inv[cb + j] > 0.f) {
-                                const uint64_t key = make_key(__uint_as_float(v[j]) * inv[cb + j], (uint32_t)(row0 + cb + j));
-                                const uint32_t i = atomicAdd(&pend_n[a], 1u);
-                                if (i < (uint32_t)kPendCap) {
-                                    pend_key[a * kPendCap + i] = key;
-                                    pend_q[a * kPendCap + i] = (uint32_t)q;
-                                } else {
-                                    append_candidate(sc, allow, q, key);
-                                }
+                    // hits: slot = the warp's running count + hitting lanes below me (no atomics, warp converged)
+                    while (__any_sync(0xffffffffu, pass != 0)) {
+                        const bool has = pass != 0;
+                        const uint32_t b = __ballot_sync(0xffffffffu, has);
+                        if (has) {
+                            const int j = __ffs(pass) - 1;
+                            pass &= pass - 1;
+                            const uint64_t key = make_key(__uint_as_float(pick16(v, j)) * inv[cb + j], (uint32_t)(row0 + cb + j));
+                            const uint32_t slot = hits + __popc(b & lt);
+                            if (slot < (uint32_t)kWarpCap) {
+                                wkey[slot] = key;
+                                wq_[slot] = (uint32_t)q;
+                            } else {
+                                append_candidate(sc, allow, q, key);
                             }
                         }
+                        hits += __popc(b);
                     }
                 }
             }
@@ -325,6 +326,7 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             __syncwarp();
             if (lane == 0) {
                 if (leader) mbar_arrive(&tmem_empty[a]); else mbar_arrive_remote(&tmem_empty[a], 0);
+                pend_n[a * kEpiWarps + wq] = hits;
                 mbar_arrive(&pend_full[a]);
             }
         }
@@ -347,7 +349,7 @@ struct QaPlan {
 bool plan_qa(int dim, QaPlan *out) {
     if (dim % (kBlockK * kKbPerStage) || dim / 2 + 2 * kAccCols > 512) return false;   // queries + 2 accumulators must fit TMEM
     const size_t fixed = 2 * kStepRows * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 +
-                         2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 1024;
+                         2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 2 * kEpiWarps * sizeof(uint32_t) + 1024;
     int stages = (int)(((size_t)kSmemBudget - fixed) / kStageBytes);
     if (stages > kMaxStages) stages = kMaxStages;
     if (stages < 4) return false;
