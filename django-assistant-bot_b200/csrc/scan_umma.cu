@@ -1,12 +1,13 @@
-// scan_umma.cu - tensor-core scoring for larger query batches over bf16 stores (tcgen05 + TMEM + TMA).
+// scan_umma.cu - tensor-core scoring for larger query batches (tcgen05 + TMEM + TMA): bf16 stores with
+// kind::f16 MMAs, fp32 stores with kind::tf32 MMAs (the kernel is a template on the store type).
 //
 // Scoring Q queries against N rows is a dense [N x D] x [D x Q] contraction; beyond a handful of
 // queries the CUDA cores cannot keep up with HBM, the 5th-gen tensor cores can.  Per CTA
 // (persistent, one per SM, cta_group::1):
-//   warp 0      TMA producer: the query block B [n_pad x D] bf16 is loaded ONCE into shared memory
+//   warp 0      TMA producer (one elected lane): the query block B [n_pad x D] bf16 is loaded ONCE into shared memory
 //               (it stays resident for the whole launch); corpus tiles A [128 rows x 64 cols] stream
 //               through a multi-stage ring (cp.async.bulk.tensor.2d, 128-byte swizzle, mbarriers)
-//   warp 1      MMA issuer: one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=n_pad, K=16)
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=n_pad, K=16)
 //               D/64 x 4 times per tile into one of two TMEM accumulator stages, then
 //               tcgen05.commit -> mbarrier frees the smem stage / publishes the accumulator
 //   warp 2      TMEM allocator (tcgen05.alloc / dealloc)

@@ -16,12 +16,16 @@
 //     publishes the accumulator to both CTAs of the pair; epilogue warps of all four CTAs drain
 //     their own TMEM half (threshold test, rare appends) while the next super-tile's MMAs run.
 //
-// HBM and L2 traffic = the corpus bytes, once per launch.  Roles per CTA (8 warps):
-//   warp 0 lane 0   TMA producer (A tiles: ranks 0 and 1 only; B quarter: every rank)
-//   warp 1 lane 0   MMA issuer (pair leaders = even ranks only)
-//   warp 2          TMEM allocator (cta_group::2, executed in both CTAs of a pair)
-//   warp 3 lane 0   tells the pair leader when this CTA's query quarter has landed
-//   warps 4-7       epilogue
+// HBM and L2 traffic = the corpus bytes, once per launch.  Roles per CTA (12 warps):
+//   warp 0, one elected lane   TMA producer (A tiles: ranks 0 and 1 only; B quarter: every rank)
+//   warp 1, one elected lane   MMA issuer (pair leaders = even ranks only)
+//   warp 2                     TMEM allocator (cta_group::2, executed in both CTAs of a pair)
+//   warp 3                     tells the pair leader when this CTA's query quarter has landed, then
+//                              flushes the epilogue warps' staged candidates to the global buffers
+//   warps 4-11                 epilogue: two warps per TMEM lane quarter, half of the pair's columns each
+// The single-lane roles are entered through elect_one() and every tcgen05/TMA operand is warp-uniform
+// (umma.cuh explains what it costs otherwise).  -DDAB_EXP_* macros build timing/ablation variants of this
+// file for tools/exp_scan.py; none is defined in the product build.
 #include <stdio.h>
 #include <stdlib.h>
 
