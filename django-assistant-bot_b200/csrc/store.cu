@@ -14,6 +14,8 @@
 #include <utility>
 #include <vector>
 
+#include <cub/device/device_scan.cuh>
+
 #include "search.cuh"
 
 namespace dab {
@@ -593,7 +595,9 @@ __global__ void delete_rows_kernel(float *__restrict__ inv_norm, const int64_t *
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
         const int64_t r = rows[i];
-        if (r >= 0 && r < size) inv_norm[r] = 0.f;   // a row with inverse norm 0 is never returned by any scan
+        // an inverse norm that is not > 0 is never returned by any scan; the sign bit tells a tombstone (-0.0)
+        // from a genuine zero vector (+0.0), which dab_store_compact must keep
+        if (r >= 0 && r < size) inv_norm[r] = __int_as_float((int)0x80000000);
     }
 }
 }  // namespace
@@ -626,5 +630,134 @@ extern "C" DAB_API int dab_store_export(dab_store *s, int64_t row0, int64_t n, v
         DAB_CUDA_OK(cudaMemcpyAsync(inv_norm_out_dev, s->inv_norm + row0, (size_t)n * sizeof(float), cudaMemcpyDeviceToDevice, st));
     if (ids_out_dev)
         DAB_CUDA_OK(cudaMemcpyAsync(ids_out_dev, s->ids + row0, (size_t)n * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+    return DAB_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Physical compaction: drop the tombstones, keep the order of the surviving rows.
+// Positions come from one exclusive scan of the "alive" flags; rows then move chunk by chunk
+// through a staging buffer (gather the chunk's survivors, then copy them down), because the
+// destination range [pos[c0], pos[c1]) may overlap the chunk's own source range but never a later one.
+namespace dab {
+namespace {
+
+constexpr uint32_t kTombstoneBits = 0x80000000u;
+
+__global__ void alive_flags_kernel(const float *__restrict__ inv_norm, int64_t n, int *__restrict__ flags) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = __float_as_uint(inv_norm[i]) != kTombstoneBits ? 1 : 0;
+    else if (i == n) flags[i] = 0;   // pos[n] = survivors
+}
+
+// one warp per row of the chunk [c0, c1): survivors go to stage[pos[i] - pos[c0]]
+__global__ void compact_gather_kernel(const unsigned char *__restrict__ rows, const float *__restrict__ inv_norm,
+                                      const int64_t *__restrict__ ids, const int *__restrict__ flags, const int *__restrict__ pos,
+                                      int64_t c0, int64_t c1, size_t row_bytes, unsigned char *__restrict__ stage_rows,
+                                      float *__restrict__ stage_inv, int64_t *__restrict__ stage_ids) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = c0 + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= c1 || !flags[i]) return;
+    const int64_t j = pos[i] - pos[c0];
+    const uint4 *src = reinterpret_cast<const uint4 *>(rows + (size_t)i * row_bytes);
+    uint4 *dst = reinterpret_cast<uint4 *>(stage_rows + (size_t)j * row_bytes);
+    for (size_t u = lane; u < row_bytes / sizeof(uint4); u += 32) dst[u] = src[u];
+    if (lane == 0) {
+        stage_inv[j] = inv_norm[i];
+        stage_ids[j] = ids[i];
+    }
+}
+
+__global__ void compact_scatter_kernel(unsigned char *__restrict__ rows, float *__restrict__ inv_norm, int64_t *__restrict__ ids,
+                                       const int *__restrict__ pos, int64_t c0, int64_t c1, size_t row_bytes,
+                                       const unsigned char *__restrict__ stage_rows, const float *__restrict__ stage_inv,
+                                       const int64_t *__restrict__ stage_ids) {
+    const int64_t d0 = pos[c0];
+    const int64_t cnt = pos[c1] - d0;
+    const size_t units = (size_t)cnt * row_bytes / sizeof(uint4);
+    const uint4 *src = reinterpret_cast<const uint4 *>(stage_rows);
+    uint4 *dst = reinterpret_cast<uint4 *>(rows + (size_t)d0 * row_bytes);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (size_t u = t; u < units; u += stride) dst[u] = src[u];
+    for (size_t j = t; j < (size_t)cnt; j += stride) {
+        inv_norm[d0 + j] = stage_inv[j];
+        ids[d0 + j] = stage_ids[j];
+    }
+}
+
+__global__ void compact_tail_kernel(float *__restrict__ inv_norm, int64_t *__restrict__ ids, const int *__restrict__ pos, int64_t n,
+                                    int64_t id_base, int renumber) {
+    const int64_t kept = pos[n];
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (i >= kept) inv_norm[i] = 0.f;              // rows past the new end read as zero vectors
+    else if (renumber) ids[i] = id_base + i;       // implicit ids stay "id_base + row"
+}
+
+struct CompactTemps {
+    int *flags = nullptr, *pos = nullptr;
+    void *cub_tmp = nullptr;
+    unsigned char *stage_rows = nullptr;
+    float *stage_inv = nullptr;
+    int64_t *stage_ids = nullptr;
+    ~CompactTemps() {
+        cudaFree(flags);
+        cudaFree(pos);
+        cudaFree(cub_tmp);
+        cudaFree(stage_rows);
+        cudaFree(stage_inv);
+        cudaFree(stage_ids);
+    }
+};
+
+}  // namespace
+}  // namespace dab
+
+extern "C" DAB_API int dab_store_compact(dab_store *s, int64_t *removed_out, void *stream) {
+    using namespace dab;
+    if (int rc = check_store(s, "dab_store_compact")) return rc;
+    std::lock_guard<std::mutex> g(s->mu);
+    if (removed_out) *removed_out = 0;
+    const int64_t n = s->size;
+    if (n == 0) return DAB_OK;
+    if (n >= (int64_t)1 << 31) return fail(DAB_E_CAPACITY, "dab_store_compact: more than 2^31 - 1 rows");
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (s->scratch_free) DAB_CUDA_OK(cudaStreamWaitEvent(st, s->scratch_free, 0));   // after every search already enqueued
+    const size_t row_bytes = (size_t)s->dim * (s->dtype == DAB_BF16 ? 2 : 4);
+    int64_t chunk = (int64_t)((size_t)256 << 20) / (int64_t)row_bytes;   // <= 256 MiB of staging
+    if (chunk > 131072) chunk = 131072;
+    if (chunk < 1) chunk = 1;
+    if (chunk > n) chunk = n;
+    CompactTemps t;
+    DAB_CUDA_OK(cudaMalloc(&t.flags, (size_t)(n + 1) * sizeof(int)));
+    DAB_CUDA_OK(cudaMalloc(&t.pos, (size_t)(n + 1) * sizeof(int)));
+    DAB_CUDA_OK(cudaMalloc(&t.stage_rows, (size_t)chunk * row_bytes));
+    DAB_CUDA_OK(cudaMalloc(&t.stage_inv, (size_t)chunk * sizeof(float)));
+    DAB_CUDA_OK(cudaMalloc(&t.stage_ids, (size_t)chunk * sizeof(int64_t)));
+    size_t cub_bytes = 0;
+    DAB_CUDA_OK(cub::DeviceScan::ExclusiveSum(nullptr, cub_bytes, t.flags, t.pos, (int)(n + 1), st));
+    DAB_CUDA_OK(cudaMalloc(&t.cub_tmp, cub_bytes ? cub_bytes : 1));
+    alive_flags_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(s->inv_norm, n, t.flags);
+    DAB_LAUNCH_OK();
+    DAB_CUDA_OK(cub::DeviceScan::ExclusiveSum(t.cub_tmp, cub_bytes, t.flags, t.pos, (int)(n + 1), st));
+    unsigned char *rows = static_cast<unsigned char *>(s->rows);
+    // dab_store_create only admits rows that are a multiple of 16 bytes, and the base is 256-byte aligned
+    for (int64_t c0 = 0; c0 < n; c0 += chunk) {
+        const int64_t c1 = c0 + chunk < n ? c0 + chunk : n;
+        compact_gather_kernel<<<(unsigned)((c1 - c0 + 7) / 8), 256, 0, st>>>(rows, s->inv_norm, s->ids, t.flags, t.pos, c0, c1, row_bytes,
+                                                                            t.stage_rows, t.stage_inv, t.stage_ids);
+        compact_scatter_kernel<<<(unsigned)(4 * s->num_sms), 256, 0, st>>>(rows, s->inv_norm, s->ids, t.pos, c0, c1, row_bytes,
+                                                                          t.stage_rows, t.stage_inv, t.stage_ids);
+        DAB_LAUNCH_OK();
+    }
+    compact_tail_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s->inv_norm, s->ids, t.pos, n, s->id_base, s->explicit_ids ? 0 : 1);
+    DAB_LAUNCH_OK();
+    int kept = 0;
+    DAB_CUDA_OK(cudaMemcpyAsync(&kept, t.pos + n, sizeof(int), cudaMemcpyDeviceToHost, st));
+    DAB_CUDA_OK(cudaStreamSynchronize(st));   // the new size is host state: this call is synchronous
+    s->size = kept;
+    if (removed_out) *removed_out = n - kept;
     return DAB_OK;
 }

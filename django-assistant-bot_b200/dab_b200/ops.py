@@ -180,6 +180,14 @@ class ChunkStore:
         with torch.cuda.device(self.device):
             check(lib().dab_store_delete_rows(self._h, rows.data_ptr(), rows.numel(), _stream(self.device)))
 
+    def compact(self) -> int:
+        """Physically drop the tombstoned rows (survivors keep their order; implicit ids are renumbered
+        to ``id_base + row``).  Synchronous; returns how many rows were removed."""
+        removed = _lib.c_int64(0)
+        with self._lock, torch.cuda.device(self.device):
+            check(lib().dab_store_compact(self._h, _lib.ctypes.byref(removed), _stream(self.device)))
+        return int(removed.value)
+
     def export(self, row0: int, n: int):
         """(rows [n,dim] in the store's dtype, inv_norm [n] fp32, ids [n] int64) copied out of the store."""
         rows = torch.empty((n, self.dim), dtype=self.dtype, device=self.device)

@@ -131,6 +131,28 @@ class DeviceTable:
         self._cols.clear()
         return len(rows)
 
+    def compact(self) -> int:
+        """Physically drop the tombstones (what VACUUM does for the table after the cascade deletes):
+        the device store moves the surviving rows down in order and the host columns follow with the
+        same survivors, so store row ``i`` is again row ``i`` of every column.  Returns rows removed."""
+        if not self._deleted:
+            return 0
+        live = self.live_mask()
+        removed = self.store.compact()
+        if removed != len(self._deleted) or len(self.store) != int(live.sum()):
+            raise DabError(1, f"compaction removed {removed} rows, {len(self._deleted)} were tombstoned")
+        keep = np.flatnonzero(live).tolist()
+        self._pks = [self._pks[i] for i in keep]
+        self._doc = [self._doc[i] for i in keep]
+        self._text = [self._text[i] for i in keep]
+        self._order = [self._order[i] for i in keep]
+        self._meta = {k: [v[i] for i in keep] for k, v in self._meta.items()}
+        self._row_of_pk = {pk: i for i, pk in enumerate(self._pks)}
+        self._deleted = set()
+        self._doc_dev = None
+        self._cols.clear()
+        return removed
+
     def live_mask(self) -> Optional[np.ndarray]:
         if not self._deleted:
             return None

@@ -114,11 +114,22 @@ DAB_API int dab_store_append(dab_store *s, const void *rows_dev, int rows_dtype,
                      int64_t n, void *stream);
 /*
  * Delete rows (tombstones): the rows stay in place but are never returned again - their stored
- * inverse norm becomes 0, which every scan treats like a zero vector.  Replaces the deletes of
+ * inverse norm becomes -0.0, which every scan treats like a zero vector.  Replaces the deletes of
  * document finalisation (older documents of a wiki removed, assistant/processing/tasks.py:67-74).
  *   rows_dev [n] int64 STORE ROW indices (not ids); out-of-range entries are ignored.
  */
 DAB_API int dab_store_delete_rows(dab_store *s, const int64_t *rows_dev, int64_t n, void *stream);
+/*
+ * Physically remove the tombstones left by dab_store_delete_rows: surviving rows keep their order and
+ * move down, their ids travel with them (explicit ids) or stay "id_base + row" (implicit ids, i.e. the
+ * rows are renumbered - a caller that keeps host columns aligned with store rows compacts those with the
+ * same survivors).  Genuine zero vectors are kept.  What VACUUM does for the table after the deletes of
+ * document finalisation (assistant/processing/tasks.py:67-74); without it every scan keeps streaming the
+ * dead rows.  Synchronous: waits for searches already enqueued on this store, allocates temporaries
+ * (8 bytes per row + <= 256 MiB of staging), returns when the store has its new size.
+ *   removed_out  number of rows dropped (may be NULL)
+ */
+DAB_API int dab_store_compact(dab_store *s, int64_t *removed_out, void *stream);
 /*
  * Copy rows [row0, row0+n) out of the store, in the store's dtype, with their inverse norms
  * (0 = deleted / zero row) and ids; any output may be NULL.  For snapshots of a shard.
