@@ -7,6 +7,11 @@ unknown model, ``{"embeddings": [[float]]}`` on success, 500 with ``str(e)`` on 
 ``/dialog/`` (LLM generation) is out of scope.  The embedder behind it pools on the B200
 (``dab_b200.embedders.B200TransformersEmbedder``).
 
+One addition, opt-in per request: a client that sends ``Accept: application/octet-stream`` gets the
+same embeddings as raw little-endian float32 (``X-Embedding-Shape: rows,dim``) instead of JSON - at
+768 floats per text the JSON text is ~6x the bytes and most of the endpoint's CPU time.  Without
+that header the reference's JSON contract is unchanged.
+
 Run like the reference (gunicorn_conf.py:9-16):
     gunicorn -k uvicorn.workers.UvicornWorker "dab_b200.gpu_service:create_app()"
 """
@@ -16,13 +21,22 @@ import logging
 from contextlib import asynccontextmanager
 from typing import Dict, Iterable, List, Optional
 
-from fastapi import FastAPI, HTTPException
+import numpy as np
+from fastapi import FastAPI, HTTPException, Request
+from fastapi.responses import Response
 from pydantic import BaseModel
 
 logger = logging.getLogger(__name__)
 
 # gpu_service/models.py:1-3 of the reference
 DEFAULT_EMBEDDER_MODELS = ["sberbank-ai/ruBert-base"]
+BINARY_MEDIA_TYPE = "application/octet-stream"
+
+
+def decode_binary_embeddings(content: bytes, shape_header: str) -> np.ndarray:
+    """Client side of the binary transport: body + ``X-Embedding-Shape`` -> [rows, dim] float32."""
+    rows, dim = (int(x) for x in shape_header.split(","))
+    return np.frombuffer(content, dtype="<f4").reshape(rows, dim)
 
 
 class EmbeddingRequest(BaseModel):
@@ -59,11 +73,20 @@ def create_app(embedder_models: Optional[Iterable[str]] = None, embedders: Optio
     app.state.embedders = registry
 
     @app.post("/embeddings/")
-    async def get_embeddings(request: EmbeddingRequest):
+    async def get_embeddings(request: EmbeddingRequest, http: Request):
         model = request.model.lower()
         if model not in registry:
             raise HTTPException(status_code=400, detail="Model is not supported")
         try:
+            if BINARY_MEDIA_TYPE in http.headers.get("accept", ""):
+                embedder = registry[model]
+                if hasattr(embedder, "embed_tensor"):     # device tensor -> one D2H copy, no Python floats
+                    arr = embedder.embed_tensor(request.texts).float().cpu().numpy() if request.texts else np.zeros((0, 0), "<f4")
+                else:
+                    arr = np.asarray(await embedder.embeddings(request.texts), dtype="<f4")
+                arr = np.ascontiguousarray(arr, dtype="<f4").reshape(len(request.texts), -1)
+                return Response(content=arr.tobytes(), media_type=BINARY_MEDIA_TYPE,
+                                headers={"X-Embedding-Shape": f"{arr.shape[0]},{arr.shape[1]}"})
             embeddings = await registry[model].embeddings(request.texts)
             return {"embeddings": embeddings}
         except Exception as e:

@@ -167,6 +167,13 @@ def test_endpoint_with_b200_embedder():
         e = np.asarray(r.json()["embeddings"])
         assert e.shape == (3, 384)
         np.testing.assert_allclose(np.linalg.norm(e, axis=1), 1.0, rtol=1e-5)
+        from dab_b200.gpu_service import BINARY_MEDIA_TYPE, decode_binary_embeddings
+        rb = c.post("/embeddings/", json={"model": "minilm", "texts": texts[:3]}, headers={"Accept": BINARY_MEDIA_TYPE})
+        assert rb.status_code == 200
+        eb = decode_binary_embeddings(rb.content, rb.headers["x-embedding-shape"])
+        assert eb.shape == (3, 384)
+        np.testing.assert_allclose(eb, e, rtol=1e-6, atol=1e-7)      # same values, fewer bytes
+        assert len(rb.content) * 3 < len(r.content)
         r = c.post("/embeddings/", json={"model": "minilm", "texts": ["not-in-the-stub-vocabulary"]})
         assert r.status_code == 500        # tokenizer KeyError surfaces as HTTP 500 with str(e)
 

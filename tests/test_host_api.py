@@ -85,6 +85,24 @@ def test_embeddings_endpoint_contract():
         assert c.post("/embeddings/", json={"model": "bad"}).status_code == 422
 
 
+def test_embeddings_endpoint_binary_transport_is_opt_in():
+    """Accept: application/octet-stream -> raw float32 + shape header; the JSON contract stays the default."""
+    from fastapi.testclient import TestClient
+    from dab_b200.gpu_service import BINARY_MEDIA_TYPE, create_app, decode_binary_embeddings
+    app = create_app(embedders={"m": _GoodEmbedder(), "bad": _BadEmbedder()})
+    with TestClient(app) as c:
+        r = c.post("/embeddings/", json={"model": "m", "texts": ["ab", "abcd", ""]}, headers={"Accept": BINARY_MEDIA_TYPE})
+        assert r.status_code == 200 and r.headers["content-type"] == BINARY_MEDIA_TYPE
+        assert r.headers["x-embedding-shape"] == "3,2" and len(r.content) == 3 * 2 * 4
+        np.testing.assert_array_equal(decode_binary_embeddings(r.content, r.headers["x-embedding-shape"]),
+                                      np.asarray([[2, 1], [4, 1], [0, 1]], dtype=np.float32))
+        assert c.post("/embeddings/", json={"model": "m", "texts": ["ab"]}).json() == {"embeddings": [[2.0, 1.0]]}
+        r = c.post("/embeddings/", json={"model": "bad", "texts": ["x"]}, headers={"Accept": BINARY_MEDIA_TYPE})
+        assert r.status_code == 500 and r.json()["detail"] == "device on fire"
+        r = c.post("/embeddings/", json={"model": "nope", "texts": ["x"]}, headers={"Accept": BINARY_MEDIA_TYPE})
+        assert r.status_code == 400
+
+
 def test_endpoint_skips_models_that_fail_to_load():
     from fastapi.testclient import TestClient
     from dab_b200.gpu_service import create_app
