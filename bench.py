@@ -373,6 +373,11 @@ def main():
     roof["search_ms_per_search"] = search_ms
     roof["scan_launches_per_search"] = prof["scan_launches"] / max(1, args.steps)
     roof["peak_source"] = peaks["source"]
+    if roof["bound"] == "hbm":
+        roof["peak_note"] = "the HBM peak is the driver's COPY measurement (read + write); a read-only scan can run a few per cent above it"
+    else:
+        roof["peak_note"] = ("the tensor peak is cuBLAS bf16 under the sustained power cap; this kernel also streams the whole shard "
+                             "from HBM and runs power-capped (see clocks.reasons)")
     roof["traffic"] = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):

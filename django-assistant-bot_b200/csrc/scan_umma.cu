@@ -163,7 +163,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
             mbar_wait_bounded(&tmem_full[a], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pad);
-            epilogue_tile(taddr, (nq + 15) & ~15, rinv, row, tau_s, q0, allow, sc);
+            epilogue_tile_wl(taddr, (nq + 15) & ~15, rinv, row, tau_s, q0, allow, sc, WarpList{nullptr, nullptr, 0});
             row = row_next;
             rinv = rinv_next;
             tc_fence_before();

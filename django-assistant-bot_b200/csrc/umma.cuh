@@ -106,16 +106,6 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity
 }
 
 
-// Shared-memory staging list for admitted candidates: epilogue threads drop (key, query) pairs here
-// with a shared-memory atomic and move on; a separate warp does the global-memory part (exact
-// threshold test, row filter, atomicAdd on the query's counter, store) off the critical path.
-struct PendList {
-    uint64_t *key;
-    uint32_t *q;
-    uint32_t *n;   // entries offered (may exceed cap: the overflow was appended directly)
-    int cap;
-};
-
 __device__ __forceinline__ void append_candidate(const SearchScratch &sc, const uint32_t *__restrict__ allow, int q, uint64_t key) {
     const uint32_t row = key_row(key);
     if (allow != nullptr && !((allow[row >> 5] >> (row & 31)) & 1u)) return;
@@ -125,66 +115,10 @@ __device__ __forceinline__ void append_candidate(const SearchScratch &sc, const 
     }
 }
 
-// One 16-column slab of an accumulator row: threshold test for 16 queries, rare appends.
-__device__ __forceinline__ void epilogue_slab(const uint32_t (&v)[16], int c0, float rinv, long long row, const float *tau_s,
-                                              int q_base, const uint32_t *__restrict__ allow, const SearchScratch &sc,
-                                              const PendList *pend = nullptr) {
-    uint32_t pass = 0;
-#pragma unroll
-    for (int j = 0; j < 16; j += 4) {
-        const float4 tq = *reinterpret_cast<const float4 *>(tau_s + c0 + j);
-        pass |= (__uint_as_float(v[j + 0]) * rinv >= tq.x ? 1u : 0u) << (j + 0);
-        pass |= (__uint_as_float(v[j + 1]) * rinv >= tq.y ? 1u : 0u) << (j + 1);
-        pass |= (__uint_as_float(v[j + 2]) * rinv >= tq.z ? 1u : 0u) << (j + 2);
-        pass |= (__uint_as_float(v[j + 3]) * rinv >= tq.w ? 1u : 0u) << (j + 3);
-    }
-    if (pass && rinv > 0.f) {
-        // slow path (rare once thresholds exist)
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            if (pass & (1u << j)) {
-                const int q = q_base + c0 + j;
-                const uint64_t key = make_key(__uint_as_float(v[j]) * rinv, (uint32_t)row);
-                if (pend != nullptr) {
-                    const uint32_t i = atomicAdd(pend->n, 1u);
-                    if (i < (uint32_t)pend->cap) {
-                        pend->key[i] = key;
-                        pend->q[i] = (uint32_t)q;
-                        continue;
-                    }
-                }
-                append_candidate(sc, allow, q, key);
-            }
-        }
-    }
-}
-
-// Drains this thread's accumulator row (TMEM lane) over `ncols` query columns (a multiple of 16,
-// uniform across the warp).  The tcgen05.ld of the next slab is in flight while the current one is
-// tested, so TMEM latency is paid once per tile, not once per slab.
-__device__ __forceinline__ void epilogue_tile(uint32_t taddr, int ncols, float rinv, long long row, const float *tau_s,
-                                              int q_base, const uint32_t *__restrict__ allow, const SearchScratch &sc,
-                                              const PendList *pend = nullptr) {
-    if (ncols <= 0) return;
-    uint32_t v0[16], v1[16];
-    tmem_ld16(taddr, v0);
-    for (int c0 = 0; c0 < ncols; c0 += 32) {
-        tmem_ld_wait();
-        const bool second = c0 + 16 < ncols;
-        if (second) tmem_ld16(taddr + (uint32_t)(c0 + 16), v1);
-        epilogue_slab(v0, c0, rinv, row, tau_s, q_base, allow, sc, pend);
-        if (second) {
-            tmem_ld_wait();
-            if (c0 + 32 < ncols) tmem_ld16(taddr + (uint32_t)(c0 + 32), v0);
-            epilogue_slab(v1, c0 + 16, rinv, row, tau_s, q_base, allow, sc, pend);
-        }
-    }
-}
-
 // ---- staging without atomics -------------------------------------------------------------------
-// The admitted-candidate path above costs a shared-memory atomic (and a 16-way divergent branch ladder)
-// per hit; at ~1 hit per 1000 scores that was most of the epilogue's time once the MMAs ran at their
-// floor.  Here every epilogue warp owns a list: the slot of a hit is the warp's running count (a
+// Admitting a candidate used to cost a shared-memory atomic and a 16-way divergent branch ladder per
+// hit; at ~1 hit per 1000 scores that was most of the epilogue's time once the MMAs ran at their
+// floor.  Here every epilogue warp owns a list (cap 0 = no list, hits go straight to the candidate buffer): the slot of a hit is the warp's running count (a
 // warp-uniform register) plus the number of hitting lanes below it (one ballot) - no atomics, no
 // divergent ladder; the loop below runs once per "some lane still has a hit", all lanes converged.
 struct WarpList {
