@@ -394,15 +394,17 @@ def main():
         return
     value = Q * args.steps / (ms_total * 1e-3)
     e2e_val = Q * args.steps / (ms_e2e * 1e-3)
+    kernel_path = store.describe_plan(Q, k)["path"]          # what the library actually ran
+    tensor = kernel_path != "simt"
     line = dict(metric="exact cosine top-k queries/sec", value=value, unit="queries/s", n_gpus=world, steps=args.steps,
                 warmup=args.warmup, ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="strong",
-                vs_baseline=None, dtype=("bf16" if w["dtype"] == "bf16" else "tf32") if Q > 4 else "f32", data="synthetic",
+                vs_baseline=None, dtype=("bf16" if w["dtype"] == "bf16" else "tf32") if tensor else "f32", data="synthetic",
                 config={"workload": args.workload, "desc": w["desc"], "rows": N, "rows_per_gpu": n_local, "dim": D,
-                        "store_dtype": w["dtype"], "Q": Q, "k": k, "path": args.path, "exchange": exchange,
+                        "store_dtype": w["dtype"], "Q": Q, "k": k, "path": args.path, "kernel_path": kernel_path, "exchange": exchange,
                         "arithmetic": ("bf16 x bf16 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
-                                       if w["dtype"] == "bf16" and Q > 4 else
+                                       if w["dtype"] == "bf16" and tensor else
                                        "tf32 x tf32 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
-                                       if Q > 4 else "fp32 FMA dot products"),
+                                       if tensor else "fp32 FMA dot products"),
                         "l2": "inputs larger than L2: every step streams the whole shard "
                               f"({n_local * D * elem / 1e9:.2f} GB >> 126 MB L2)"},
                 e2e=dict(value=e2e_val, unit="queries/s", h2d_bytes_per_step=Q * D * 4, d2h_bytes_per_step=Q * k * 12,

@@ -270,6 +270,7 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
         // path below when the round overflowed or is a retry (duplicates), when fewer than k
         // candidates exist, or when the kept set would not fit.
         bool fast_done = false;
+        bool gave_up = false;   // thread 0: exactness is lost for this query, retrying the round cannot help
         if (margin > 0.f && !ovf && !ctrl->retry && n >= k) {
             fast_done = compact_select(keys, mine, n, k, k_cap, margin, &sc.cand_count[qi], &sc.tau_key[qi]);
         }
@@ -323,7 +324,13 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
                     sc.tau_key[qi] = thr_key;
                     // more rows inside the margin than we can keep: the exactness guarantee is gone
                     // (sorted keys were left unread, or more unique keys than slots, or the buffer itself overflowed)
-                    if (s_keep == u && u == k_cap && (base < n || kept_total > k_cap || ovf)) atomicExch(&ctrl->inexact, 1);
+                    if (s_keep == u && u == k_cap && (base < n || kept_total > k_cap || ovf)) {
+                        atomicExch(&ctrl->inexact, 1);
+                        // Everything kept sits inside the margin, so the threshold cannot tighten: a re-scan would
+                        // overflow again, forever.  Let the search finish; its verdict is DAB_E_INEXACT and the
+                        // caller repeats it on the CUDA-core path.
+                        gave_up = true;
+                    }
                 }
             } else if (tid == 0) {
                 sc.tau_key[qi] = kTauMin;
@@ -333,8 +340,9 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
         }
         }  // !fast_done
         if (tid == 0) {
-            sc.overflowed[qi] = ovf ? 1 : 0;
-            if (ovf) atomicExch(&ctrl->any_overflow, 1);
+            const bool again = ovf && !gave_up;
+            sc.overflowed[qi] = again ? 1 : 0;
+            if (again) atomicExch(&ctrl->any_overflow, 1);
         }
     }
     // ---- round control by the last CTA

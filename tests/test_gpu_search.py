@@ -118,6 +118,7 @@ def test_search_clustered_corpus_overflows_and_recovers():
     q = torch.randn(1, D, generator=g)
     store = ops.ChunkStore(N, D, torch.float32, DEV)
     store.append(rows.to(DEV))
+    store.set_path("simt")          # the CUDA-core path reports the overflow as such; auto is covered below
     plan = store.describe_plan(1, k)
     assert plan["path"] == "simt" and plan["num_levels"] >= 2
     r = torch.arange(100_000, 130_000)
@@ -129,6 +130,20 @@ def test_search_clustered_corpus_overflows_and_recovers():
     rc = _lib.lib().dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
     assert rc == _lib.DAB_E_INCOMPLETE and (i == -1).all() and torch.isnan(s).all()
     _check(store, rows.numpy(), q, k)
+    # auto path (tensor cores for this layout): the raw call may say incomplete or inexact (29k rows sit inside
+    # the rescoring margin), never OK with a wrong answer; the checked search must still be exact
+    store.set_path("auto")
+    assert store.describe_plan(1, k)["path"] == "tcgen05"
+    s, i = store.search_async(q.to(DEV), k)
+    rc = _lib.lib().dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
+    assert rc in (_lib.DAB_E_INCOMPLETE, _lib.DAB_E_INEXACT), rc
+    _check(store, rows.numpy(), q, k)
+    # the inexact verdict is remembered: the next 64 few-query searches go straight to the CUDA cores
+    # (no wasted tensor attempt on a corpus this dense), then the tensor path is probed again
+    assert store.describe_plan(1, k)["path"] == "simt" and store.describe_plan(64, k)["path"] == "tcgen05"
+    for _ in range(64):
+        store.search_async(q.to(DEV), k)
+    assert store.describe_plan(1, k)["path"] == "tcgen05"
     store.close()
 
 
