@@ -45,6 +45,7 @@ constexpr int kWarpCap = 64;        // staged candidates per epilogue warp per t
 constexpr int kPendCap = kEpiWarps * kWarpCap;
 constexpr int kSuperRows = 2 * kTileRows;  // corpus rows per MMA pair step (UMMA M = 256)
 constexpr int kSmemBudget = 227 * 1024 - 2048;
+template <bool F32>   // F32: fp32 store and fp32 queries through kind::tf32 (a k-block is 128 bytes = 32 elements)
 __global__ void __launch_bounds__(kThreads, 1)
 scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_constant__ CUtensorMap tmap_q, StoreView sv,
                       const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pair, int stages,
@@ -66,8 +67,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     const int nq = max(0, min(n_pair, nq_all - pair * n_pair));
 
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int num_kb = sv.dim / kBlockK;
-    const int b_kb_bytes = n_half * kBlockK * 2;
+    constexpr int kb_elems = F32 ? kBlockK / 2 : kBlockK;
+    const int num_kb = sv.dim / kb_elems;
+    const int b_kb_bytes = n_half * 128;
     unsigned char *b_smem = smem;                                              // [num_kb][n_half rows x 128 B]
     unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;              // [stages][128 rows x 128 B]
     float *tau_s = reinterpret_cast<float *>(a_smem + (size_t)stages * kAStageBytes);  // [256]
@@ -120,7 +122,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             // this CTA's quarter of the query block: rows [pair*n_pair + half*n_half, +n_half) of the bf16 copy
             mbar_arrive_expect_tx(b_full, (uint32_t)(num_kb * b_kb_bytes));
             for (int kb = 0; kb < num_kb; kb++)
-                tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kBlockK, pair * n_pair + half * n_half, b_full);
+                tma_load_2d(b_smem + (size_t)kb * b_kb_bytes, &tmap_q, kb * kb_elems, pair * n_pair + half * n_half, b_full);
             if (rank < 2) {
                 // A tiles for the whole cluster: my 128-row half of every super-tile, multicast to my
                 // twin in the other pair
@@ -146,9 +148,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
 #endif
 
                         if (num_pairs == 2)
-                            tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s], mask);
+                            tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s], mask);
                         else
-                            tma_load_2d_2cta(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kBlockK, row0, &full[s]);
+                            tma_load_2d_2cta(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s]);
                         if (++s == stages) { s = 0; ph ^= 1u; }
                     }
                 }
@@ -160,7 +162,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     } else if (warp == 1) {
         if (leader && elect_one()) {
             // ------------------------------------------------------------ MMA issuer of the pair
-            const uint32_t idesc = make_idesc(n_pair, kSuperRows);
+            const uint32_t idesc = F32 ? make_idesc_tf32(n_pair, kSuperRows) : make_idesc(n_pair, kSuperRows);
             const uint16_t pair_mask = (uint16_t)(0x3u << (2 * pair));
             mbar_wait_bounded(b_pair, 0);
             tc_fence_after();
@@ -205,7 +207,10 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
 #endif
 #pragma unroll
                     for (int k = 0; k < DAB_EXP_MMAS; k++)
-                        umma_f16_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                        if constexpr (F32)
+                            umma_tf32_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                        else
+                            umma_f16_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
 #ifdef DAB_EXP_COMMIT_EVERY
                     if (kb % DAB_EXP_COMMIT_EVERY == DAB_EXP_COMMIT_EVERY - 1)
 #endif
@@ -310,11 +315,11 @@ struct QuadPlan {
 };
 
 // n_pair = queries per CTA pair (multiple of 32: each CTA's share of B must be a multiple of 16 rows)
-bool plan_quad(int dim, int nq, int num_pairs, QuadPlan *out) {
+bool plan_quad(int dim, int nq, int num_pairs, int elem_bytes, QuadPlan *out) {
     int n_pair = ((nq + num_pairs - 1) / num_pairs + 31) / 32 * 32;
     if (n_pair < 32) n_pair = 32;
     if (n_pair > 128) return false;
-    const size_t b_bytes = (size_t)(n_pair / 2) * dim * 2;
+    const size_t b_bytes = (size_t)(n_pair / 2) * dim * elem_bytes;
     const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 + 2 * kEpiWarps * sizeof(uint32_t) +
                          2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
@@ -333,17 +338,34 @@ bool plan_quad(int dim, int nq, int num_pairs, QuadPlan *out) {
 
 int quad_tile_rows() { return kSuperRows; }
 
+static int quad_elem_bytes(int dtype) { return dtype == DAB_BF16 ? 2 : 4; }
+static bool quad_layout_ok(int dim, int dtype) {
+    return (dtype == DAB_BF16 || dtype == DAB_F32) && (dim * quad_elem_bytes(dtype)) % 128 == 0;
+}
+
+// bf16 stores (kind::f16) and fp32 stores (kind::tf32); rows must be whole 128-byte k-blocks
 bool quad_supported(int dim, int dtype, int nq) {
     QuadPlan p;
-    return dtype == DAB_BF16 && dim % kBlockK == 0 && nq >= 1 && nq <= DAB_MAX_QUERY_BATCH && plan_quad(dim, nq, 2, &p);
+    return quad_layout_ok(dim, dtype) && nq >= 1 && nq <= DAB_MAX_QUERY_BATCH && plan_quad(dim, nq, 2, quad_elem_bytes(dtype), &p);
+}
+
+// the most queries one 4-CTA cluster (two pairs) can score per corpus pass; 0 if the layout is unsupported
+int quad_queries_per_pass(int dim, int dtype) {
+    int best = 0;
+    QuadPlan p;
+    if (!quad_layout_ok(dim, dtype)) return 0;
+    for (int n = 64; n <= DAB_MAX_QUERY_BATCH; n += 64)
+        if (plan_quad(dim, n, 2, quad_elem_bytes(dtype), &p)) best = n;
+    return best;
 }
 
 // the most queries ONE pair (cluster of 2, no multicast) can score per corpus pass
-int pair_queries_per_pass(int dim) {
+int pair_queries_per_pass(int dim, int dtype) {
     int best = 0;
     QuadPlan p;
+    if (!quad_layout_ok(dim, dtype)) return 0;
     for (int n = 32; n <= 256; n += 32)
-        if (plan_quad(dim, n, 1, &p)) best = n;
+        if (plan_quad(dim, n, 1, quad_elem_bytes(dtype), &p)) best = n;
     return best;
 }
 
@@ -352,15 +374,19 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     QuadPlan qp;
     if (num_pairs != 1 && num_pairs != 2) return fail(DAB_E_INVALID, "scan_umma_quad: 1 or 2 pairs per cluster");
     const int kCluster = 2 * num_pairs;
-    if (sv.dtype != DAB_BF16 || sv.dim % kBlockK || !plan_quad(sv.dim, nq, num_pairs, &qp))
-        return fail(DAB_E_INVALID, "scan_umma_quad: needs a bf16 store, dim % 64 == 0 and <= 256 queries that fit shared memory");
+    const bool f32 = sv.dtype == DAB_F32;
+    if (!quad_layout_ok(sv.dim, sv.dtype) || !plan_quad(sv.dim, nq, num_pairs, quad_elem_bytes(sv.dtype), &qp))
+        return fail(DAB_E_INVALID, "scan_umma_quad: needs rows of whole 128-byte blocks (bf16 or fp32) and a query block that fits shared memory");
     if (plan.tile_rows != kSuperRows) return fail(DAB_E_INVALID, "scan_umma_quad: level plan built for another tile size");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
-    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows)) return rc;
-    if (int rc = make_map(&tmap_q, sc.qsplit + (size_t)q0 * sv.dim, (uint64_t)(2 * DAB_MAX_QUERY_BATCH - q0), (uint64_t)sv.dim,
-                          (uint32_t)(qp.n_pair / 2)))
-        return rc;
-    DAB_CUDA_OK(cudaFuncSetAttribute(scan_umma_quad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qp.smem));
+    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
+    // B = the unit-norm fp32 queries (fp32 stores) or their bf16 copy (bf16 stores); rows past the buffer read as zero
+    const void *qbase = f32 ? static_cast<const void *>(sc.qhat + (size_t)q0 * sv.dim)
+                            : static_cast<const void *>(sc.qsplit + (size_t)q0 * sv.dim);
+    const uint64_t q_rows = (uint64_t)((f32 ? DAB_MAX_QUERY_BATCH : 2 * DAB_MAX_QUERY_BATCH) - q0);
+    if (int rc = make_map(&tmap_q, qbase, q_rows, (uint64_t)sv.dim, (uint32_t)(qp.n_pair / 2), f32)) return rc;
+    auto kernel = f32 ? scan_umma_quad_kernel<true> : scan_umma_quad_kernel<false>;
+    DAB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qp.smem));
     // how many 4-CTA clusters can be resident at once (GPC shapes strand a few SMs)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(num_sms / kCluster * kCluster), 1, 1);
@@ -375,7 +401,7 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     int max_clusters = 0;
-    DAB_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_clusters, scan_umma_quad_kernel, &cfg));
+    DAB_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_clusters, kernel, &cfg));
     if (max_clusters < 1) return fail(DAB_E_CUDA, "scan_umma_quad: no 4-CTA cluster fits on this device");
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
@@ -389,7 +415,7 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
         fprintf(stderr, "[dab] quad: pairs=%d nq=%d n_pair=%d stages=%d tmem_cols=%d smem=%zu max_clusters=%d clusters=%lld levels=%d\n", num_pairs, nq,
                 qp.n_pair, qp.stages, qp.tmem_cols, qp.smem, max_clusters, clusters, plan.num_levels);
     cfg.gridDim = dim3((unsigned)(clusters * kCluster), 1, 1);
-    DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, scan_umma_quad_kernel, tmap_rows, tmap_q, sv, allow, sc, q0, nq, qp.n_pair, qp.stages,
+    DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, tmap_rows, tmap_q, sv, allow, sc, q0, nq, qp.n_pair, qp.stages,
                                    qp.tmem_cols, num_pairs, acc, plan));
     count_launch();
     return DAB_OK;

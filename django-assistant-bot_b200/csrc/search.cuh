@@ -63,7 +63,8 @@ int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScr
 // wide query blocks (up to 256): 4-CTA clusters, cta_group::2 MMA pairs, multicast corpus tiles
 int quad_tile_rows();
 bool quad_supported(int dim, int dtype, int nq);
-int pair_queries_per_pass(int dim);
+int quad_queries_per_pass(int dim, int dtype);
+int pair_queries_per_pass(int dim, int dtype = DAB_BF16);
 // num_pairs = 2: one 4-CTA cluster scores up to 256 queries per pass (tiles multicast to both pairs);
 // num_pairs = 1: a 2-CTA cluster scores up to pair_queries_per_pass(dim) queries, every tile byte delivered once
 int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,

@@ -310,6 +310,7 @@ struct SearchPlan {
     int path;        // 1 = CUDA cores, 2 = tcgen05
     bool quad;       // tcgen05: cluster kernel (cta_group::2 pairs) for query blocks wider than one SM holds
     int pairs;       // cluster kernel: 2 = 4-CTA cluster, tiles multicast to both pairs; 1 = one pair per cluster
+    int quad_chunk;  // cluster kernel: queries per launch (the whole block unless it exceeds one cluster's shared memory)
     bool qa;         // tcgen05: queries-as-A pair kernel for wide query blocks (preferred when it applies)
     int k_cap;       // candidates kept per query between levels
     float margin;    // tensor path: approximate-score margin that is kept for rescoring
@@ -344,14 +345,23 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
         const bool wide = nq > umma_queries_per_pass(dim, dtype);
         sp.qa = wide && use_qa && qa_supported(dim, dtype, nq);
         sp.quad = wide && !sp.qa && !no_quad && quad_supported(dim, dtype, nq);
+        sp.quad_chunk = nq;
+        // fp32 rows are twice as wide: one cluster holds 192 queries at dim 768, so a 256-query block takes two
+        // corpus passes of 128 (still far better than slicing it six ways through the single-CTA kernel)
+        const int quad_cap = quad_queries_per_pass(dim, dtype);
+        if (wide && !sp.qa && !no_quad && !sp.quad && quad_cap > 0 && nq > quad_cap) {
+            const int passes = (nq + quad_cap - 1) / quad_cap;
+            sp.quad = true;
+            sp.quad_chunk = ((nq + passes - 1) / passes + 63) / 64 * 64;
+        }
         // up to pair_queries_per_pass (128 at dim 768) ONE pair holds the whole block: 74 two-CTA clusters use every
         // SM, every corpus byte goes to one SM, N = 128 MMAs run at their floor - 2.9 ms per 12.5M x 768 shard at
         // Q = 100..128 against 3.6-3.7 ms for the 4-CTA form (whose N = 64 MMAs are issue-bound); two pair passes
         // for Q = 256 cost 6.0 ms against 4.7 ms.  It also beats the single-CTA kernel once that one's epilogue gets
         // long (Q = 80: 2.89 vs 3.00 ms, Q = 96: 2.91 vs 3.25 ms; equal at Q <= 64).  DAB_PAIR_MIN_Q moves the switch.
         static const int pair_min_q = getenv("DAB_PAIR_MIN_Q") ? atoi(getenv("DAB_PAIR_MIN_Q")) : 65;
-        if (!sp.qa && !no_quad && dtype == DAB_BF16 && nq <= pair_queries_per_pass(dim) && quad_supported(dim, dtype, nq) &&
-            (wide || nq >= pair_min_q)) {
+        if (!sp.qa && !no_quad && nq <= pair_queries_per_pass(dim, dtype) && quad_supported(dim, dtype, nq) &&
+            (wide || (dtype == DAB_BF16 && nq >= pair_min_q))) {
             sp.quad = true;
             sp.pairs = 1;
         } else {
@@ -386,8 +396,13 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
                     if (int rc = launch_scan_umma_qa(sv, allow, sc, 0, nq, plan, s->num_sms, st)) return rc;
                 } else if (sp.quad && sp.pairs == 1) {
                     if (int rc = launch_scan_umma_quad(sv, allow, sc, 0, nq, plan, s->num_sms, st, 1)) return rc;
+                } else if (sp.quad && sp.quad_chunk < nq) {
+                    for (int q0 = 0; q0 < nq; q0 += sp.quad_chunk)
+                        if (int rc = launch_scan_umma_quad(sv, allow, sc, q0, nq - q0 < sp.quad_chunk ? nq - q0 : sp.quad_chunk, plan,
+                                                           s->num_sms, st))
+                            return rc;
                 } else if (sp.quad && pair_mode) {
-                    const int per = pair_queries_per_pass(sv.dim);
+                    const int per = pair_queries_per_pass(sv.dim, sv.dtype);
                     for (int q0 = 0; q0 < nq; q0 += per)
                         if (int rc = launch_scan_umma_quad(sv, allow, sc, q0, nq - q0 < per ? nq - q0 : per, plan, s->num_sms, st, 1))
                             return rc;

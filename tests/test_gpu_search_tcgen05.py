@@ -108,7 +108,7 @@ def test_tf32_tensor_path_on_fp32_stores(N, D, Q, k):
     queries[0] = rows[11]
     store = ops.ChunkStore(N, D, torch.float32, DEV)
     store.append(rows.to(DEV))
-    assert store.describe_plan(Q, k)["path"] == "tcgen05"        # auto: tensor cores once Q > 4
+    assert store.describe_plan(Q, k)["path"].startswith("tcgen05")   # auto: tensor cores (single-CTA or cluster kernel)
     scores, ids = store.search(queries.to(DEV), k)
     S = search_ref.exact_scores(rows.numpy(), queries.numpy())
     ids, scores = ids.cpu().numpy(), scores.cpu().numpy()
@@ -118,6 +118,29 @@ def test_tf32_tensor_path_on_fp32_stores(N, D, Q, k):
     store.set_path("simt")
     s2, i2 = store.search(queries.to(DEV), k)
     np.testing.assert_array_equal(i2.cpu().numpy(), ids)
+    store.close()
+
+
+@pytest.mark.parametrize("N,D,Q,k", [(60_000, 768, 64, 10), (60_000, 768, 96, 20), (50_000, 768, 150, 10),
+                                     (40_000, 768, 256, 10), (30_000, 384, 256, 5), (70_001, 1024, 100, 50)])
+def test_tf32_cluster_kernel_on_fp32_stores(N, D, Q, k):
+    """fp32 stores with more queries than one SM holds (48 at dim 768): the cluster kernel with kind::tf32 -
+    one pair up to 96 queries, two pairs up to 192, two corpus passes of 128 for a 256-query block."""
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(N + D + Q + k)
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    rows[N // 3] = 0
+    queries[Q - 1] = rows[17]
+    store = ops.ChunkStore(N, D, torch.float32, DEV)
+    store.append(rows.to(DEV))
+    assert store.describe_plan(Q, k)["path"] == "tcgen05-cluster"
+    scores, ids = store.search(queries.to(DEV), k)
+    S = search_ref.exact_scores(rows.numpy(), queries.numpy())
+    ids, scores = ids.cpu().numpy(), scores.cpu().numpy()
+    for qi in range(Q):
+        search_ref.check_topk_parity(S[qi], ids[qi], scores[qi], k)
+    assert ids[Q - 1, 0] == 17
     store.close()
 
 
