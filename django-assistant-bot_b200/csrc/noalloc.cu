@@ -117,7 +117,7 @@ extern "C" DAB_API int dab_search_noalloc(const void *rows_dev, int rows_dtype, 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (n_rows == 0) return launch_fill_empty(out_scores_dev, out_ids_dev, (int64_t)Q * k, st);
 
-    SearchScratch sc;
+    SearchScratch sc{};
     sc.qhat = reinterpret_cast<float *>(d->scratch + kOffQhat);
     sc.qsplit = nullptr;  // only the tensor path uses it; this entry point scores on CUDA cores
     sc.cand = reinterpret_cast<uint64_t *>(d->scratch + kOffCand);

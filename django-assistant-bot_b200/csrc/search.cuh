@@ -18,6 +18,7 @@ struct SearchScratch {
     uint64_t *tau_key;      // [256] current admission threshold (a kept candidate's key)
     int *active;            // [256] query takes part in the current round
     int *overflowed;        // [256] query overflowed in the current round
+    int *inexact_q;         // [256] tensor path: more rows inside the margin than kept -> outputs poisoned (may be null)
     SearchCtrl *ctrl;
 };
 

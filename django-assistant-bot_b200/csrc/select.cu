@@ -18,6 +18,7 @@ size_t search_scratch_bytes(int dim) {
     b += up(DAB_MAX_QUERY_BATCH * sizeof(uint64_t));                          // tau_key
     b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // active
     b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // overflowed
+    b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // inexact_q
     b += up(sizeof(SearchCtrl));
     return b;
 }
@@ -39,6 +40,8 @@ SearchScratch carve_scratch(void *base, int dim) {
     s.active = reinterpret_cast<int *>(p);
     p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
     s.overflowed = reinterpret_cast<int *>(p);
+    p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
+    s.inexact_q = reinterpret_cast<int *>(p);
     p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
     s.ctrl = reinterpret_cast<SearchCtrl *>(p);
     return s;
@@ -110,6 +113,7 @@ search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int 
         sc.tau_key[qi] = kTauMin;
         sc.active[qi] = 1;
         sc.overflowed[qi] = 0;
+        if (sc.inexact_q) sc.inexact_q[qi] = 0;
         if (qi == 0) {
             SearchCtrl c = {};
             if (!first_chunk) {  // a later chunk of the same search call keeps the sticky verdicts
@@ -326,6 +330,7 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
                     // (sorted keys were left unread, or more unique keys than slots, or the buffer itself overflowed)
                     if (s_keep == u && u == k_cap && (base < n || kept_total > k_cap || ovf)) {
                         atomicExch(&ctrl->inexact, 1);
+                        if (sc.inexact_q) sc.inexact_q[qi] = 1;   // this query's outputs get poisoned; the others stay valid
                         // Everything kept sits inside the margin, so the threshold cannot tighten: a re-scan would
                         // overflow again, forever.  Let the search finish; its verdict is DAB_E_INEXACT and the
                         // caller repeats it on the CUDA-core path.
@@ -409,10 +414,13 @@ finish_rescore_kernel(SearchScratch sc, StoreView sv, int k, int k_keep, int num
     extern __shared__ uint64_t keys[];  // [pow2 >= k_keep]
     const int qi = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool done = sc.ctrl->cur_level >= num_levels;
+    // a query with more rows inside the rescoring margin than could be kept is answered with poison (NaN, -1):
+    // the caller sees DAB_E_INEXACT and repeats exactly those queries on the CUDA-core path; the rest are final
+    const bool lost = sc.inexact_q != nullptr && sc.inexact_q[qi] != 0;
+    const bool done = sc.ctrl->cur_level >= num_levels && !lost;
     const int cnt = done ? min((int)sc.cand_count[qi], k_keep) : 0;
     if (qi == 0 && tid == 0) {
-        if (!done) sc.ctrl->sticky_incomplete = 1;
+        if (sc.ctrl->cur_level < num_levels) sc.ctrl->sticky_incomplete = 1;
         if (sc.ctrl->inexact) sc.ctrl->sticky_inexact = 1;
     }
     int P = 32;

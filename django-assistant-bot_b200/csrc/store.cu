@@ -598,24 +598,46 @@ extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, 
     int rc = DAB_OK;
     for (int q0 = 0; q0 < Q && rc == DAB_OK; q0 += DAB_MAX_QUERY_BATCH) {
         const int nq = Q - q0 < DAB_MAX_QUERY_BATCH ? Q - q0 : DAB_MAX_QUERY_BATCH;
-        const size_t qbytes = (size_t)nq * s->dim * sizeof(float);
-        memcpy(hbase + L.q, q_host + (size_t)q0 * s->dim, qbytes);
+        memcpy(hbase + L.q, q_host + (size_t)q0 * s->dim, (size_t)nq * s->dim * sizeof(float));
         int spare = 0;
         bool forced = false;
+        int nrun = nq;              // queries in the staging block: the chunk, or its poisoned queries on the exact redo
+        std::vector<int> redo;
         for (;;) {
-            if ((rc = cudaMemcpyAsync(dbase + L.q, hbase + L.q, qbytes, cudaMemcpyHostToDevice, st)) != cudaSuccess) {
+            if ((rc = cudaMemcpyAsync(dbase + L.q, hbase + L.q, (size_t)nrun * s->dim * sizeof(float), cudaMemcpyHostToDevice, st)) != cudaSuccess) {
                 rc = fail(DAB_E_CUDA, std::string("dab_store_search_host: H2D: ") + cudaGetErrorString((cudaError_t)rc));
                 break;
             }
-            rc = dab_store_search(s, reinterpret_cast<const float *>(dbase + L.q), nq, k, allow_bitmap_dev,
+            rc = dab_store_search(s, reinterpret_cast<const float *>(dbase + L.q), nrun, k, allow_bitmap_dev,
                                   reinterpret_cast<float *>(dbase + L.scores), reinterpret_cast<int64_t *>(dbase + L.ids), st);
             if (rc != DAB_OK) break;
-            cudaMemcpyAsync(hbase + L.scores, dbase + L.scores, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, st);
-            cudaMemcpyAsync(hbase + L.ids, dbase + L.ids, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
+            cudaMemcpyAsync(hbase + L.scores, dbase + L.scores, (size_t)nrun * k * sizeof(float), cudaMemcpyDeviceToHost, st);
+            cudaMemcpyAsync(hbase + L.ids, dbase + L.ids, (size_t)nrun * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
             rc = dab_store_search_status(s, st);   // synchronises the stream: results and verdict are on the host
-            if (rc == DAB_E_INEXACT && !forced) {   // answer this call on the exact CUDA-core path
+            if (rc == DAB_E_INEXACT && !forced) {
+                // Only the queries whose margin overflowed came back poisoned (NaN score in front); the others are
+                // final.  Keep those, pack the poisoned ones to the front of the staging block and answer them on
+                // the exact CUDA-core path.
                 forced = true;
                 s->path = 1;
+                const float *hs = reinterpret_cast<const float *>(hbase + L.scores);
+                const int64_t *hi = reinterpret_cast<const int64_t *>(hbase + L.ids);
+                redo.clear();
+                for (int q = 0; q < nq; q++) {
+                    if (hs[(size_t)q * k] != hs[(size_t)q * k]) {
+                        redo.push_back(q);
+                    } else {
+                        memcpy(out_scores_host + (size_t)(q0 + q) * k, hs + (size_t)q * k, (size_t)k * sizeof(float));
+                        memcpy(out_ids_host + (size_t)(q0 + q) * k, hi + (size_t)q * k, (size_t)k * sizeof(int64_t));
+                    }
+                }
+                if (redo.empty() || (int)redo.size() == nq) {   // nothing to tell apart: redo the whole chunk
+                    redo.clear();
+                    continue;
+                }
+                for (size_t j = 0; j < redo.size(); j++)
+                    memcpy(hbase + L.q + j * s->dim * sizeof(float), q_host + (size_t)(q0 + redo[j]) * s->dim, (size_t)s->dim * sizeof(float));
+                nrun = (int)redo.size();
                 continue;
             }
             if (rc == DAB_E_INCOMPLETE && spare < 64) {   // adversarial row order: retry with spare rounds
@@ -627,9 +649,14 @@ extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, 
         }
         s->spare_rounds = saved_spare;
         s->path = saved_path;
-        if (rc == DAB_OK) {
+        if (rc == DAB_OK && redo.empty()) {
             memcpy(out_scores_host + (size_t)q0 * k, hbase + L.scores, (size_t)nq * k * sizeof(float));
             memcpy(out_ids_host + (size_t)q0 * k, hbase + L.ids, (size_t)nq * k * sizeof(int64_t));
+        } else if (rc == DAB_OK) {
+            for (size_t j = 0; j < redo.size(); j++) {
+                memcpy(out_scores_host + (size_t)(q0 + redo[j]) * k, hbase + L.scores + j * k * sizeof(float), (size_t)k * sizeof(float));
+                memcpy(out_ids_host + (size_t)(q0 + redo[j]) * k, hbase + L.ids + j * k * sizeof(int64_t), (size_t)k * sizeof(int64_t));
+            }
         }
     }
     return rc;

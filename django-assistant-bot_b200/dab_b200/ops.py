@@ -259,19 +259,30 @@ class ChunkStore:
         with self._lock:
             spare = 0
             forced_simt = False
+            kept = None
             try:
                 while True:
                     scores, ids = self.search_async(queries, k, allow_bitmap)
                     with torch.cuda.device(self.device):
                         rc = lib().dab_store_search_status(self._h, _stream(self.device))
                     if rc == _lib.DAB_E_INEXACT and not forced_simt:
-                        # more rows inside the bf16 rescoring margin than the tensor pass can keep:
-                        # answer this call on the exact CUDA-core path instead
+                        # more rows inside the rescoring margin than the tensor pass can keep, for SOME queries:
+                        # those came back poisoned (NaN score in front), the others are final.  Answer the
+                        # poisoned ones on the exact CUDA-core path and splice them in.
                         lib().dab_store_set_path(self._h, 1)
                         forced_simt = True
+                        bad = torch.isnan(scores[:, 0])
+                        n_bad = int(bad.sum())
+                        if 0 < n_bad < scores.shape[0]:
+                            kept = (scores, ids, bad)
+                            queries = (queries if queries.dim() == 2 else queries[None, :])[bad].contiguous()
                         continue
                     if rc != _lib.DAB_E_INCOMPLETE:
                         check(rc)
+                        if kept is not None:
+                            kept[0][kept[2]] = scores
+                            kept[1][kept[2]] = ids
+                            return kept[0], kept[1]
                         return scores, ids
                     spare = 4 if spare == 0 else spare * 2
                     if spare > 64:

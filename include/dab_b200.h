@@ -51,7 +51,9 @@ typedef struct dab_store dab_store;
 #define DAB_E_DIM 3         /* "different vector dimensions", like pgvector raises */
 #define DAB_E_CAPACITY 4    /* store full / size beyond a stated maximum */
 #define DAB_E_INCOMPLETE 5  /* a search did not finish its scan rounds (see dab_store_search_status) */
-#define DAB_E_INEXACT 6     /* tensor path: too many rows inside the rescoring margin; use the CUDA-core path */
+#define DAB_E_INEXACT 6     /* tensor path: for some queries more rows lie inside the rescoring margin than it keeps;
+                             * exactly those queries come back poisoned (score NaN, id -1), every other query of the
+                             * call is final; repeat the poisoned ones with dab_store_set_path(s, 1) */
 
 /* limits */
 #define DAB_MAX_K 2048           /* largest n of a search; the reference uses 1, 5, 10, 250 */
@@ -160,7 +162,7 @@ DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, con
  * (`_objects_embedding_search` receives the query as a Python list, search_service.py:186).
  * Copies the queries to the device (pinned staging owned by the store, allocated on first use),
  * searches, copies scores/ids back, synchronises `stream`, and repeats internally if the device
- * reported DAB_E_INCOMPLETE (spare rounds) or DAB_E_INEXACT (CUDA-core path).  Synchronous.
+ * reported DAB_E_INCOMPLETE (spare rounds) or DAB_E_INEXACT (the poisoned queries alone, on the CUDA-core path).  Synchronous.
  */
 DAB_API int dab_store_search_host(dab_store *s, const float *q_host, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
                                   float *out_scores_host, int64_t *out_ids_host, void *stream);

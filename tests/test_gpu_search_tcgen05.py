@@ -68,14 +68,46 @@ def test_tcgen05_inexact_falls_back_to_exact_path():
     store.set_path("tcgen05")
     store.set_spare_rounds(8)
     store.append(rows.to(DEV))
-    store.search_async(queries.to(DEV), k)
+    raw_s, raw_i = store.search_async(queries.to(DEV), k)
     rc = _lib.lib().dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
     assert rc == _lib.DAB_E_INEXACT, _lib.lib().dab_last_error()
-    store.set_spare_rounds(0)
-    scores, ids = store.search(queries.to(DEV), k)
     S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), queries.numpy())
+    # only the query whose margin overflowed is poisoned; the other seven answers of the raw call are final
+    assert torch.isnan(raw_s[0]).all() and (raw_i[0] == -1).all()
+    for qi in range(1, Q):
+        search_ref.check_topk_parity(S[qi], raw_i[qi].cpu().numpy(), raw_s[qi].cpu().numpy(), k)
+    store.set_spare_rounds(0)
+    scores, ids = store.search(queries.to(DEV), k)           # checked: redoes query 0 alone on the CUDA cores
     for qi in range(Q):
         search_ref.check_topk_parity(S[qi], ids[qi].cpu().numpy(), scores[qi].cpu().numpy(), k)
+    hs, hi = store.search_host(queries.numpy(), k)            # the C host entry splices the same way
+    np.testing.assert_array_equal(hi, ids.cpu().numpy())
+    np.testing.assert_array_equal(hs, scores.cpu().numpy())
+    store.close()
+
+
+def test_inexact_query_in_a_wide_block_is_redone_alone():
+    """200 queries, one of them with 5000 near-copies in the corpus: the checked searches keep the 199 tensor-path
+    answers and repeat only the overflowing query on the CUDA cores (not 50 CUDA-core passes for the block)."""
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(33)
+    N, D, Q, k = 60_000, 768, 200, 10
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    idx = torch.randperm(N, generator=g)[:5000]
+    rows[idx] = queries[3] + 0.001 * torch.randn(5000, D, generator=g)
+    store = ops.ChunkStore(N, D, torch.bfloat16, DEV)
+    store.append(rows.to(DEV))
+    S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), queries.numpy())
+    from dab_b200 import _lib
+    n0 = _lib.lib().dab_launch_count()
+    scores, ids = store.search(queries.to(DEV), k)
+    n1 = _lib.lib().dab_launch_count()
+    hs, hi = store.search_host(queries.numpy(), k)
+    for qi in range(Q):
+        search_ref.check_topk_parity(S[qi], ids[qi].cpu().numpy(), scores[qi].cpu().numpy(), k)
+    np.testing.assert_array_equal(hi, ids.cpu().numpy())
+    assert n1 - n0 < 60, n1 - n0       # one tensor search + one single-query exact search, not 50 passes of 4
     store.close()
 
 
