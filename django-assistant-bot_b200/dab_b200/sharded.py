@@ -145,8 +145,11 @@ class ShardedStore:
 
     def _search_p2p(self, queries: torch.Tensor, k: int, allow_bitmap):
         from ._lib import lib
-        Q = queries.shape[0] if queries.dim() == 2 else 1
+        if queries.dim() == 1:
+            queries = queries[None, :]
+        Q = queries.shape[0]
         spare, forced_simt = 0, False
+        kept = None
         try:
             while True:
                 slot = self.peer.next_slot(Q, k)
@@ -154,10 +157,26 @@ class ShardedStore:
                 s, i = self.peer.merge(Q, k, lib().dab_store_status_dev(self.local._h))
                 incomplete, inexact = self.peer.verdict()          # same answer on every rank
                 if inexact and not forced_simt:
+                    # Some rank's tensor pass could not keep every row inside the rescoring margin for SOME
+                    # queries; that rank's lists for them are poisoned (NaN in front).  The union over the ranks
+                    # (every rank is here: the verdict is OR-ed) is repeated on the exact CUDA-core path by all
+                    # ranks together; the other queries' merged answers are final.
                     lib().dab_store_set_path(self.local._h, 1)
                     forced_simt = True
+                    bad = torch.isnan(slot[0][:, 0]).to(torch.int32)
+                    dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=self.group)
+                    bad = bad.bool()
+                    n_bad = int(bad.sum())
+                    if 0 < n_bad < Q:
+                        kept = (s, i, bad)
+                        queries = queries[bad].contiguous()
+                        Q = n_bad
                     continue
                 if not incomplete:
+                    if kept is not None:
+                        kept[0][kept[2]] = s
+                        kept[1][kept[2]] = i
+                        return kept[0], kept[1]
                     return s, i
                 spare = 4 if spare == 0 else spare * 2
                 if spare > 64:

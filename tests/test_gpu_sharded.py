@@ -36,6 +36,19 @@ for mode in ("p2p", "nccl"):
     results[mode] = (s.cpu(), i.cpu())
     st.close()
 assert torch.equal(results["p2p"][1], results["nccl"][1]) and torch.equal(results["p2p"][0], results["nccl"][0])
+# one query with 5000 near-copies, all in rank 0's shard: its margin overflows there only; both exchanges must
+# repeat that query alone on the exact path, on every rank, and agree with the oracle
+idx = torch.randperm(N // 2, generator=g)[:5000]
+rows[idx] = queries[5] + 0.001 * torch.randn(5000, D, generator=g)
+S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), queries.numpy())
+for mode in ("p2p", "nccl"):
+    st = sharded.ShardedStore(N, D, torch.bfloat16, torch.device("cuda", rank), exchange=mode)
+    st.append_local(rows[st.lo:st.hi].cuda())
+    for rep in range(2):
+        s, i = st.search(queries.cuda(), 10)
+        for q in range(Q):
+            search_ref.check_topk_parity(S[q], i[q].cpu().numpy(), s[q].cpu().numpy(), 10)
+    st.close()
 dist.barrier(); dist.destroy_process_group(); print("rank", rank, "ok")
 '''
 
