@@ -55,7 +55,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
 
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     constexpr int kb_elems = F32 ? kBlockK / 2 : kBlockK;    // elements per 128-byte k-block
-    const int num_kb = sv.dim / kb_elems;
+    const int num_kb = (sv.dim + kb_elems - 1) / kb_elems;   // a partial last k-block is zero-filled by TMA (both operands)
     const int b_kb_bytes = n_pad * 128;                   // one k-block of the query operand
     unsigned char *b_smem = smem;                          // [num_kb][n_pad rows x 128 B]
     unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;  // [stages][128 rows x 128 B]
@@ -186,7 +186,7 @@ struct UmmaPlan {
 
 bool plan_umma(int dim, int nq, int elem_bytes, UmmaPlan *out) {
     const int n_pad = nq <= 16 ? 16 : (nq + 15) / 16 * 16;
-    const size_t b_bytes = (size_t)n_pad * dim * elem_bytes;
+    const size_t b_bytes = (size_t)n_pad * (((size_t)dim * elem_bytes + 127) / 128 * 128);   // whole 128-byte k-blocks
     const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 8) * sizeof(uint64_t) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
     int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
@@ -207,11 +207,13 @@ int elem_bytes_of(int dtype) { return dtype == DAB_BF16 ? 2 : 4; }
 
 int umma_tile_rows() { return kTileRows; }
 
-// bf16 stores (kind::f16) and fp32 stores (kind::tf32); a row must be a whole number of 128-byte k-blocks
+// bf16 stores (kind::f16) and fp32 stores (kind::tf32).  Rows need not be whole 128-byte k-blocks: the tensor maps
+// describe the true row length and TMA zero-fills the tail of the last k-block of both operands (row pitch % 16 == 0
+// is what the tensor map needs, and dab_store_create guarantees it)
 bool umma_supported(int dim, int dtype) {
     UmmaPlan p;
     if (dtype != DAB_BF16 && dtype != DAB_F32) return false;
-    return (dim * elem_bytes_of(dtype)) % 128 == 0 && plan_umma(dim, 16, elem_bytes_of(dtype), &p);
+    return (dim * elem_bytes_of(dtype)) % 16 == 0 && plan_umma(dim, 16, elem_bytes_of(dtype), &p);
 }
 
 // the widest query block whose copy stays resident in shared memory next to >= 4 corpus stages
@@ -228,7 +230,7 @@ void umma_release_maps(void *) {}
 int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq, const LevelPlan &plan,
                      int num_sms, cudaStream_t st) {
     if (!umma_supported(sv.dim, sv.dtype))
-        return fail(DAB_E_INVALID, "scan_umma: needs a bf16 (dim % 64 == 0) or fp32 (dim % 32 == 0) store");
+        return fail(DAB_E_INVALID, "scan_umma: needs a bf16 or fp32 store whose query block fits shared memory");
     if (plan.tile_rows != kTileRows) return fail(DAB_E_INVALID, "scan_umma: level plan built for another tile size");
     const bool f32 = sv.dtype == DAB_F32;
     const int eb = elem_bytes_of(sv.dtype);

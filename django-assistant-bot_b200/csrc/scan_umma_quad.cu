@@ -68,7 +68,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
 
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     constexpr int kb_elems = F32 ? kBlockK / 2 : kBlockK;
-    const int num_kb = sv.dim / kb_elems;
+    const int num_kb = (sv.dim + kb_elems - 1) / kb_elems;   // partial last k-block: zero-filled by TMA
     const int b_kb_bytes = n_half * 128;
     unsigned char *b_smem = smem;                                              // [num_kb][n_half rows x 128 B]
     unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;              // [stages][128 rows x 128 B]
@@ -319,7 +319,7 @@ bool plan_quad(int dim, int nq, int num_pairs, int elem_bytes, QuadPlan *out) {
     int n_pair = ((nq + num_pairs - 1) / num_pairs + 31) / 32 * 32;
     if (n_pair < 32) n_pair = 32;
     if (n_pair > 128) return false;
-    const size_t b_bytes = (size_t)(n_pair / 2) * dim * elem_bytes;
+    const size_t b_bytes = (size_t)(n_pair / 2) * (((size_t)dim * elem_bytes + 127) / 128 * 128);
     const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 + 2 * kEpiWarps * sizeof(uint32_t) +
                          2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
@@ -340,10 +340,10 @@ int quad_tile_rows() { return kSuperRows; }
 
 static int quad_elem_bytes(int dtype) { return dtype == DAB_BF16 ? 2 : 4; }
 static bool quad_layout_ok(int dim, int dtype) {
-    return (dtype == DAB_BF16 || dtype == DAB_F32) && (dim * quad_elem_bytes(dtype)) % 128 == 0;
+    return (dtype == DAB_BF16 || dtype == DAB_F32) && (dim * quad_elem_bytes(dtype)) % 16 == 0;
 }
 
-// bf16 stores (kind::f16) and fp32 stores (kind::tf32); rows must be whole 128-byte k-blocks
+// bf16 stores (kind::f16) and fp32 stores (kind::tf32); a partial last k-block is zero-filled by TMA
 bool quad_supported(int dim, int dtype, int nq) {
     QuadPlan p;
     return quad_layout_ok(dim, dtype) && nq >= 1 && nq <= DAB_MAX_QUERY_BATCH && plan_quad(dim, nq, 2, quad_elem_bytes(dtype), &p);
@@ -376,7 +376,7 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     const int kCluster = 2 * num_pairs;
     const bool f32 = sv.dtype == DAB_F32;
     if (!quad_layout_ok(sv.dim, sv.dtype) || !plan_quad(sv.dim, nq, num_pairs, quad_elem_bytes(sv.dtype), &qp))
-        return fail(DAB_E_INVALID, "scan_umma_quad: needs rows of whole 128-byte blocks (bf16 or fp32) and a query block that fits shared memory");
+        return fail(DAB_E_INVALID, "scan_umma_quad: needs a bf16 or fp32 store and a query block that fits shared memory");
     if (plan.tile_rows != kSuperRows) return fail(DAB_E_INVALID, "scan_umma_quad: level plan built for another tile size");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
     if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;

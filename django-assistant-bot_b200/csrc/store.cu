@@ -245,7 +245,7 @@ extern "C" DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds) {
 extern "C" DAB_API int dab_store_set_path(dab_store *s, int path) {
     if (int rc = check_store(s, "dab_store_set_path")) return rc;
     if (path < 0 || path > 2) return fail(DAB_E_INVALID, "dab_store_set_path: 0 auto, 1 CUDA cores, 2 tcgen05");
-    if (path == 2 && !umma_supported(s->dim, s->dtype)) return fail(DAB_E_INVALID, "dab_store_set_path: tcgen05 path needs a bf16 store with dim % 64 == 0 or an fp32 store with dim % 32 == 0");
+    if (path == 2 && !umma_supported(s->dim, s->dtype)) return fail(DAB_E_INVALID, "dab_store_set_path: the query block of this store does not fit shared memory on the tcgen05 path (rows too wide)");
     std::lock_guard<std::mutex> g(s->mu);
     s->path = path;
     return DAB_OK;
@@ -323,7 +323,7 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
     // auto: the tensor path whenever the row layout allows it - measured faster than the CUDA-core kernel at every
     // query count, 1 included (12.5M x 768 bf16: 2.7 ms vs 3.3 / 6.5 / 9.3 ms at Q = 1 / 2 / 4; fp32 via tf32:
     // 2.5 ms vs 2.8 / 4.1 / 5.7 ms), and no slower on stores of a few thousand rows.  The CUDA-core kernel
-    // serves row sizes that are not whole 128-byte k-blocks and is the exact fallback for DAB_E_INEXACT.
+    // is the exact fallback for DAB_E_INEXACT and serves rows too wide for a resident query block.
     if (sp.path == 0) {
         sp.path = umma_supported(dim, dtype) ? 2 : 1;
         if (sp.path == 2 && s->small_simt_credit > 0 && nq <= simt_queries_per_pass(dim, dtype)) sp.path = 1;

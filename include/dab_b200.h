@@ -172,7 +172,7 @@ DAB_API int dab_store_search_status(dab_store *s, void *stream);
 /* extra scan rounds enqueued per search for overflow retries (default 0) */
 DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds);
 /* scoring path: 0 = auto, 1 = CUDA-core fp32 dot products, 2 = tcgen05 tensor tiles (bf16 stores: kind::f16,
- * fp32 stores: kind::tf32; rows must be whole 128-byte blocks) + exact fp32 rescoring.  Auto takes the tensor
+ * fp32 stores: kind::tf32; any row length the store accepts) + exact fp32 rescoring.  Auto takes the tensor
  * path whenever the row layout allows it, for any number of queries; after a DAB_E_INEXACT verdict on a search
  * of <= 4 queries the next 64 such searches use the CUDA cores directly. */
 DAB_API int dab_store_set_path(dab_store *s, int path);

@@ -118,11 +118,30 @@ def test_auto_path_picks_tensor_cores_for_batches():
     np.testing.assert_allclose(sc_auto, sc_simt, rtol=1e-5, atol=1e-6)
 
 
-def test_tcgen05_rejected_when_rows_are_not_whole_k_blocks():
-    from dab_b200 import DabError, ops
-    store = ops.ChunkStore(100, 100, torch.float32, DEV)       # 400-byte rows: not a multiple of 128 bytes
-    with pytest.raises(DabError, match="tcgen05 path needs"):
-        store.set_path("tcgen05")
+@pytest.mark.parametrize("dtype,N,D,Q,k", [(torch.float32, 30_000, 100, 3, 10), (torch.float32, 50_000, 300, 16, 10),
+                                           (torch.bfloat16, 40_000, 104, 5, 10), (torch.bfloat16, 60_000, 1000, 40, 20),
+                                           (torch.bfloat16, 50_000, 760, 200, 10), (torch.float32, 40_000, 700, 100, 5),
+                                           (torch.bfloat16, 300, 8, 2, 5), (torch.float32, 5000, 4, 1, 3)])
+def test_tensor_path_on_rows_that_are_not_whole_k_blocks(dtype, N, D, Q, k):
+    """Row lengths that are not a multiple of 128 bytes (GloVe's 300, 1000, ...): the tensor maps carry the true
+    row length and TMA zero-fills the tail of the last k-block of rows and queries alike."""
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(N + D + Q + k)
+    rows = torch.randn(N, D, generator=g)
+    queries = torch.randn(Q, D, generator=g)
+    queries[0] = rows[9]
+    store = ops.ChunkStore(N, D, dtype, DEV)
+    store.append(rows.to(DEV))
+    assert store.describe_plan(Q, k)["path"].startswith("tcgen05")
+    scores, ids = store.search(queries.to(DEV), k)
+    S = search_ref.exact_scores(rows.to(dtype).float().numpy(), queries.numpy())
+    ids, scores = ids.cpu().numpy(), scores.cpu().numpy()
+    for qi in range(Q):
+        search_ref.check_topk_parity(S[qi], ids[qi], scores[qi], k)
+    assert ids[0, 0] == 9
+    store.set_path("simt")
+    s2, i2 = store.search(queries.to(DEV), k)
+    np.testing.assert_array_equal(i2.cpu().numpy(), ids)
     store.close()
 
 
