@@ -86,16 +86,18 @@ def test_tcgen05_inexact_falls_back_to_exact_path():
     store.close()
 
 
-def test_inexact_query_in_a_wide_block_is_redone_alone():
-    """200 queries, one of them with 5000 near-copies in the corpus: the checked searches keep the 199 tensor-path
-    answers and repeat only the overflowing query on the CUDA cores (not 50 CUDA-core passes for the block)."""
+@pytest.mark.parametrize("Q,victim", [(200, 3), (300, 280)])
+def test_inexact_query_in_a_wide_block_is_redone_alone(Q, victim):
+    """Many queries, one of them with 5000 near-copies in the corpus: the checked searches keep the other tensor-path
+    answers and repeat only the overflowing query on the CUDA cores (not 50 CUDA-core passes for the block).  With
+    300 queries the victim sits in the second 256-query chunk of the call."""
     from dab_b200 import ops
     g = torch.Generator().manual_seed(33)
-    N, D, Q, k = 60_000, 768, 200, 10
+    N, D, k = 60_000, 768, 10
     rows = torch.randn(N, D, generator=g)
     queries = torch.randn(Q, D, generator=g)
     idx = torch.randperm(N, generator=g)[:5000]
-    rows[idx] = queries[3] + 0.001 * torch.randn(5000, D, generator=g)
+    rows[idx] = queries[victim] + 0.001 * torch.randn(5000, D, generator=g)
     store = ops.ChunkStore(N, D, torch.bfloat16, DEV)
     store.append(rows.to(DEV))
     S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), queries.numpy())
@@ -107,7 +109,7 @@ def test_inexact_query_in_a_wide_block_is_redone_alone():
     for qi in range(Q):
         search_ref.check_topk_parity(S[qi], ids[qi].cpu().numpy(), scores[qi].cpu().numpy(), k)
     np.testing.assert_array_equal(hi, ids.cpu().numpy())
-    assert n1 - n0 < 60, n1 - n0       # one tensor search + one single-query exact search, not 50 passes of 4
+    assert n1 - n0 < 80, n1 - n0       # tensor search(es) + one single-query exact search, not 50+ passes of 4
     store.close()
 
 
