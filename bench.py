@@ -30,7 +30,7 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for _p in (ROOT, os.path.join(ROOT, "django-assistant-bot_b200")):
+for _p in (ROOT, os.path.join(ROOT, "django-assistant-bot_b200"), os.path.join(ROOT, "tools")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
@@ -194,18 +194,234 @@ def run_reference_arm(args, w, rank, world):
         c_oracle.search(rows, q[:nq], w["k"], nthreads=threads)
         if i >= args.warmup:
             times.append(time.perf_counter() - t0)
-    per_query_full = statistics.mean(times) / nq * (w["rows"] / n_s)
+    step_s = statistics.mean(times)
+    per_query_full = step_s / nq * (w["rows"] / n_s)
     val = 1.0 / per_query_full
-    sample = (f"per step {nq} queries over a {n_s}-row sample; per-query time scaled linearly to {w['rows']} rows "
-              f"(pgvector scans one query at a time: Q queries = Q passes)")
+    sample = (f"per step {nq} queries over a {n_s}-row sample ({step_s * 1e3:.1f} ms measured per step); per-query time scaled "
+              f"linearly to {w['rows']} rows = {per_query_full * 1e3:.0f} ms/query, i.e. {per_query_full * w['Q']:.1f} s for the "
+              f"{w['Q']}-query batch (pgvector scans one query at a time: Q queries = Q passes)")
+    # ms_per_step is what one step of THIS run took (the bounded sample); `value` is the extrapolation
     line = dict(metric="exact cosine top-k queries/sec", value=val, unit="queries/s", n_gpus=args.gpus, steps=args.steps,
-                warmup=args.warmup, ms_per_step=per_query_full * w["Q"] * 1e3, higher_is_better=True, scaling="strong",
+                warmup=args.warmup, ms_per_step=step_s * 1e3, higher_is_better=True, scaling="strong",
                 vs_baseline=None, dtype="f32", data="synthetic", impl="reference",
-                config={"workload": args.workload, "desc": w["desc"], "rows": w["rows"], "dim": w["dim"],
-                        "store_dtype": w["dtype"], "Q": w["Q"], "k": w["k"]},
+                config=search_config(args, w, w["rows"] // max(1, args.gpus)),
+                engine=dict(path="cpu", kernel_path="oracle/scan_ref.c (OpenMP)", exchange="none",
+                            arithmetic="fp32 running sums, double division (pgvector <=> restatement)"),
+                extrapolated=dict(rows_sampled=n_s, queries_sampled=nq, rows_full=w["rows"], ms_per_full_step=per_query_full * w["Q"] * 1e3),
                 cpu_baseline=dict(value=val, unit="queries/s", cores=threads, kind="port", sample=sample),
                 e2e=dict(value=val, unit="queries/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line))
+
+
+def search_config(args, w, n_local):
+    """The `config` object of a search line: the workload and nothing else, identical for our arm and the
+    reference arm (how each arm computes it is in the separate `engine` object)."""
+    elem = 2 if w["dtype"] == "bf16" else 4
+    return {"workload": args.workload, "desc": w["desc"], "rows": w["rows"], "rows_per_gpu": n_local, "dim": w["dim"],
+            "store_dtype": w["dtype"], "Q": w["Q"], "k": w["k"],
+            "l2": "inputs larger than L2: every step streams the whole shard "
+                  f"({n_local * w['dim'] * elem / 1e9:.2f} GB >> 126 MB L2)"}
+
+
+class SearchRun:
+    """One (sharded) store of a search workload plus the measurements taken on it.  Every figure of the
+    JSON line - headline and `targets` alike - comes from `measure`, i.e. from identical timing code."""
+
+    def __init__(self, env, w, exchange="auto", path="auto"):
+        self.env, self.w = env, w
+        torch, dev = env.torch, env.dev
+        from dab_b200 import sharded
+        self.N, self.D, self.k = w["rows"], w["dim"], w["k"]
+        self.sdtype = torch.bfloat16 if w["dtype"] == "bf16" else torch.float32
+        self.elem = 2 if w["dtype"] == "bf16" else 4
+        self.lo, self.hi = env.rank * self.N // env.world, (env.rank + 1) * self.N // env.world
+        self.sh = sharded.ShardedStore(self.N, self.D, self.sdtype, dev, exchange=exchange, max_q=max(w["Q"], 1),
+                                       max_k=max(self.k, 1))
+        assert (self.sh.lo, self.sh.hi) == (self.lo, self.hi)
+        self.store = self.sh.local
+        self.store.set_path(path)
+        self.exchange = "none" if env.world == 1 else ("p2p" if self.sh.peer is not None else "nccl")
+        self.sample_host = None
+        self.queries_host = gen_queries(torch, w["Q"], self.D).pin_memory()
+        self.queries_dev = self.queries_host.to(dev)
+        self._oracle = None
+
+    def blocks(self):
+        """(first global row, rows in the store dtype) of this rank's shard, regenerated block by block."""
+        torch = self.env.torch
+        r = self.lo
+        while r < self.hi:
+            b = r // BLOCK_ROWS
+            b0 = b * BLOCK_ROWS
+            blk = gen_block(torch, b, min(BLOCK_ROWS, self.N - b0), self.D, self.env.dev)
+            part = blk[r - b0: min(self.hi, b0 + BLOCK_ROWS) - b0]
+            yield r, part
+            r += part.shape[0]
+            del blk, part
+
+    def build(self, keep_cpu_sample=False):
+        import numpy as np
+        torch = self.env.torch
+        for r, part in self.blocks():
+            self.store.append(part)
+            if keep_cpu_sample and self.sample_host is None:
+                s = part[:min(part.shape[0], 250_000)]
+                self.sample_host = (s.to(torch.bfloat16).view(torch.int16).cpu().numpy().view(np.uint16)
+                                    if self.sdtype == torch.bfloat16 else s.cpu().numpy())
+        torch.cuda.synchronize()
+
+    def close(self):
+        self.sh.close()
+        self._oracle = None
+        self.env.torch.cuda.empty_cache()
+
+    # ------------------------------------------------------------------ ground truth (not timed)
+    def oracle(self):
+        """Device oracle (tools/device_oracle.py: fp32 candidate pass + float64 exact pass, plain torch) for ALL
+        queries of the workload over the whole corpus; computed once, shared by every query count measured."""
+        if self._oracle is None:
+            env, torch = self.env, self.env.torch
+            import device_oracle
+            pad = 64
+            stored = ((r, part.to(self.sdtype)) for r, part in self.blocks())
+            wi, ws = device_oracle.oracle_topk(stored, self.queries_dev, self.k, pad=pad)
+            if env.world > 1:
+                gi = [torch.empty_like(wi) for _ in range(env.world)]
+                gs = [torch.empty_like(ws) for _ in range(env.world)]
+                env.dist.all_gather(gi, wi.contiguous())
+                env.dist.all_gather(gs, ws.contiguous())
+                wi, ws = device_oracle.merge_rank_lists(gi, gs, self.k + pad)
+            self._oracle = (wi, ws)
+            torch.cuda.empty_cache()
+        return self._oracle
+
+    def verify(self, res_s, res_i, Q):
+        import device_oracle
+        wi, ws = self.oracle()
+        rep = device_oracle.parity_report(res_s[:Q], res_i[:Q], wi[:Q], ws[:Q], self.k)
+        assert rep["ok"], f"bench result disagrees with the device oracle: {rep}"
+        return (f"top-{self.k} of all {Q} quer{'y' if Q == 1 else 'ies'} match the device oracle (fp32 candidate pass + float64 "
+                f"rescoring, plain torch) over all {self.N} rows: ids position by position (near-ties < 1e-6 swapped: "
+                f"{rep['swapped_near_ties']}), scores within 1e-5 relative (worst {rep['max_rel_score_err']:.1e})")
+
+    # ------------------------------------------------------------------ timing
+    def measure(self, Q, steps, warmup, verify=True, count_launches=False):
+        env, torch, dist, L = self.env, self.env.torch, self.env.dist, self.env.L
+        from dab_b200 import ops
+        store, sh, k, D, dev, world = self.store, self.sh, self.k, self.D, self.env.dev, self.env.world
+        q_dev = self.queries_dev[:Q].contiguous()
+        q_host = self.queries_host[:Q]
+        q_np = q_host.numpy()
+        out_host_s = torch.empty(Q, k, dtype=torch.float32).pin_memory()
+        out_host_i = torch.empty(Q, k, dtype=torch.int64).pin_memory()
+        gs = torch.empty(world, Q, k, dtype=torch.float32, device=dev) if world > 1 else None
+        gi = torch.empty(world, Q, k, dtype=torch.int64, device=dev) if world > 1 else None
+        status_ptr = L.dab_store_status_dev(store._h)
+
+        def step_device():
+            if sh.peer is not None:                         # one fused publish/wait/gather/merge kernel over NVLink
+                slot = sh.peer.next_slot(Q, k)
+                store.search_async(q_dev, k, out=slot)
+                return sh.peer.merge(Q, k, status_ptr)
+            s, i = store.search_async(q_dev, k)
+            if world > 1:
+                dist.all_gather_into_tensor(gs, s)
+                dist.all_gather_into_tensor(gi, i)
+                s, i = ops.merge_topk(gs, gi)
+            return s, i
+
+        def step_e2e():
+            if world == 1:
+                # the reference-facing call: host buffers in and out through one C-ABI entry point
+                # (H2D of the queries, search, D2H of scores/ids, verdict check inside)
+                return store.search_host(q_np, k)
+            return sh.search_host(q_host, k, out=(out_host_s, out_host_i))   # pinned in, pinned out, checked
+
+        def timed(fn, n):
+            env.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                res = fn()
+            e1.record()
+            env.barrier()
+            return env.max_over_ranks(e0.elapsed_time(e1)), res
+
+        for _ in range(warmup):
+            step_device()
+        torch.cuda.synchronize()
+        status = L.dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
+        assert status == 0, f"warm-up search incomplete: {L.dab_last_error()}"
+        launches0 = L.dab_launch_count()
+        ms_total, (res_s, res_i) = timed(step_device, steps)
+        launches = L.dab_launch_count() - launches0
+        status = L.dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
+        assert status == 0, f"timed search incomplete: {L.dab_last_error()}"
+        for _ in range(warmup):          # the host-buffer path has its own first-call costs (pinned copies, lazy loads)
+            step_e2e()
+        ms_e2e, _ = timed(step_e2e, steps)
+
+        # roofline pass: the scan kernels bracketed by events on their own stream
+        store.set_profile(True)
+        env.barrier()
+        for _ in range(steps):
+            step_device()
+        prof = store.get_profile()
+        store.set_profile(False)
+        scan_ms = env.max_over_ranks(prof["scan_ms"]) / steps            # per search, slowest rank
+        search_ms = env.max_over_ranks(prof["search_ms"]) / steps
+        n_local = self.hi - self.lo
+        alg_bytes = n_local * (D * self.elem + 4) + Q * D * 4 + Q * k * 12       # SURVEY 8(d), per GPU per query batch
+        alg_flops = 2.0 * Q * n_local * D
+        peaks = env.peaks
+        out = dict(Q=Q, k=k, value=Q * steps / (ms_total * 1e-3), ms_per_step=ms_total / steps,
+                   e2e=dict(value=Q * steps / (ms_e2e * 1e-3), unit="queries/s", h2d_bytes_per_step=Q * D * 4,
+                            d2h_bytes_per_step=Q * k * 12, ms_per_step=ms_e2e / steps),
+                   scan_ms=scan_ms, search_ms=search_ms, scan_launches=prof["scan_launches"] / max(1, steps),
+                   alg_bytes=alg_bytes, alg_flops=alg_flops, launches=int(launches),
+                   kernel_path=store.describe_plan(Q, k)["path"],
+                   hbm_frac=alg_bytes / (scan_ms * 1e-3) / 1e9 / peaks["hbm"],
+                   hbm_frac_step=alg_bytes / (ms_total / steps * 1e-3) / 1e9 / peaks["hbm"],
+                   hbm_frac_e2e=alg_bytes / (ms_e2e / steps * 1e-3) / 1e9 / peaks["hbm"],
+                   tensor_frac=alg_flops / (scan_ms * 1e-3) / 1e12 / peaks["tf"])
+        out["verified"] = self.verify(res_s, res_i, Q) if verify else None
+        out["_res"] = (res_s, res_i)          # the last timed search's answer (dropped before printing)
+        return out
+
+    def roofline(self, m):
+        """The `roofline` object of the line from one measurement."""
+        peaks, w = self.env.peaks, self.w
+        t_hbm, t_tf = m["alg_bytes"] / (peaks["hbm"] * 1e9), m["alg_flops"] / (peaks["tf"] * 1e12)
+        if t_tf > t_hbm and w["dtype"] == "bf16":
+            roof = dict(bound="tensor", achieved=m["alg_flops"] / (m["scan_ms"] * 1e-3) / 1e12, peak=peaks["tf"], unit="TFLOP/s")
+            roof["hbm_frac"] = m["hbm_frac"]
+        else:
+            roof = dict(bound="hbm", achieved=m["alg_bytes"] / (m["scan_ms"] * 1e-3) / 1e9, peak=peaks["hbm"], unit="GB/s")
+        roof["frac"] = roof["achieved"] / roof["peak"]
+        roof["kernel"] = "scan (all level launches of one search)"
+        roof["scan_ms_per_search"] = m["scan_ms"]
+        roof["search_ms_per_search"] = m["search_ms"]
+        roof["scan_launches_per_search"] = m["scan_launches"]
+        roof["peak_source"] = peaks["source"]
+        if roof["bound"] == "hbm":
+            roof["peak_note"] = "the HBM peak is the driver's COPY measurement (read + write); a read-only scan can run a few per cent above it"
+        else:
+            roof["peak_note"] = ("the tensor peak is cuBLAS bf16 under the sustained power cap; this kernel also streams the whole shard "
+                                 "from HBM and runs power-capped (see clocks.reasons)")
+        roof["traffic"] = None
+        return roof
+
+    def target(self, m):
+        """Compact form of a measurement for the `targets` object."""
+        return dict(Q=m["Q"], k=m["k"], rows=self.N, rows_per_gpu=self.hi - self.lo, dim=self.D, store_dtype=self.w["dtype"],
+                    value=m["value"], unit="queries/s", ms_per_step=m["ms_per_step"], e2e=m["e2e"]["value"],
+                    e2e_ms_per_step=m["e2e"]["ms_per_step"], scan_ms=m["scan_ms"], hbm_frac=m["hbm_frac"],
+                    hbm_frac_step=m["hbm_frac_step"], hbm_frac_e2e=m["hbm_frac_e2e"], tensor_frac=m["tensor_frac"],
+                    kernel_path=m["kernel_path"], exchange=self.exchange, verified=m["verified"])
+
+
+class Env:
+    pass
 
 
 def main():
@@ -220,6 +436,7 @@ def main():
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="N>1: how local top-k lists are exchanged")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--no-targets", action="store_true", help="headline only: skip the `targets` sub-measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     w = dict(WORKLOADS[args.workload])
@@ -233,7 +450,6 @@ def main():
         run_reference_arm(args, w, rank, world)
         return
 
-    import numpy as np
     import torch
     import torch.distributed as dist
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
@@ -241,9 +457,11 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    from dab_b200 import _lib, ops
-    peaks = load_peaks()
-    L = _lib.lib()
+    from dab_b200 import _lib
+    env = Env()
+    env.torch, env.dist, env.dev, env.rank, env.world = torch, dist, dev, rank, world
+    env.peaks = load_peaks()
+    env.L = _lib.lib()
 
     def barrier():
         if world > 1:
@@ -257,214 +475,87 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    env.barrier, env.max_over_ranks = barrier, max_over_ranks
+
     if w["kind"] == "pool":
-        return bench_pool(args, w, rank, world, dev, peaks, barrier, max_over_ranks)
+        return bench_pool(args, w, rank, world, dev, env.peaks, barrier, max_over_ranks)
 
-    # ------------------------------------------------------------------ build the sharded store
-    N, D, Q, k = w["rows"], w["dim"], w["Q"], w["k"]
-    sdtype = torch.bfloat16 if w["dtype"] == "bf16" else torch.float32
-    lo, hi = rank * N // world, (rank + 1) * N // world          # contiguous row shard, ids = global row index
-    from dab_b200 import sharded
-    sh = sharded.ShardedStore(N, D, sdtype, dev, exchange=args.exchange, max_q=max(Q, 1), max_k=max(k, 1))
-    assert (sh.lo, sh.hi) == (lo, hi)
-    store = sh.local
-    store.set_path(args.path)
-    exchange = "none" if world == 1 else ("p2p" if sh.peer is not None else "nccl")
-    sample_host = None
-    r = lo
-    while r < hi:
-        b = r // BLOCK_ROWS
-        b0 = b * BLOCK_ROWS
-        blk = gen_block(torch, b, min(BLOCK_ROWS, N - b0), D, dev)
-        part = blk[r - b0: min(hi, b0 + BLOCK_ROWS) - b0]
-        store.append(part)
-        if rank == 0 and sample_host is None and not args.no_cpu_baseline and world == 1:
-            s = part[:min(part.shape[0], 250_000)]
-            sample_host = (s.to(torch.bfloat16).view(torch.int16).cpu().numpy().view(np.uint16) if sdtype == torch.bfloat16
-                           else s.cpu().numpy())
-        r += part.shape[0]
-        del blk, part
-    torch.cuda.synchronize()
-    queries_host = gen_queries(torch, Q, D).pin_memory()
-    queries_dev = queries_host.to(dev)
-    out_host_s = torch.empty(Q, k, dtype=torch.float32).pin_memory()
-    out_host_i = torch.empty(Q, k, dtype=torch.int64).pin_memory()
-    gs = torch.empty(world, Q, k, dtype=torch.float32, device=dev) if world > 1 else None
-    gi = torch.empty(world, Q, k, dtype=torch.int64, device=dev) if world > 1 else None
+    verify = not args.no_verify
+    targets = {}
+    with_targets = args.workload == DEFAULT_WORKLOAD and not args.no_targets and not args.rows
+    # ------------------------------------------------------------------ N=1: the single-GPU configs first
+    # configs[1] and configs[2] do not fit beside the 154 GB store of configs[3]: measured and freed before it is built
+    if with_targets and world == 1:
+        for name in ("c2", "c3"):
+            sw = dict(WORKLOADS[name])
+            run = SearchRun(env, sw, path=args.path)
+            run.build()
+            m = run.measure(sw["Q"], args.steps, args.warmup, verify=verify)
+            m.pop("_res")
+            targets[name] = dict(run.target(m), desc=sw["desc"])
+            run.close()
+            del run
 
-    status_ptr = L.dab_store_status_dev(store._h)
-
-    def step_device():
-        if sh.peer is not None:                         # one fused publish/wait/gather/merge kernel over NVLink
-            slot = sh.peer.next_slot(Q, k)
-            store.search_async(queries_dev, k, out=slot)
-            return sh.peer.merge(Q, k, status_ptr)
-        s, i = store.search_async(queries_dev, k)
-        if world > 1:
-            dist.all_gather_into_tensor(gs, s)
-            dist.all_gather_into_tensor(gi, i)
-            s, i = ops.merge_topk(gs, gi)
-        return s, i
-
-    queries_np = queries_host.numpy()
-
-    def step_e2e():
-        if world == 1:
-            # the reference-facing call: host buffers in and out through one C-ABI entry point
-            # (H2D of the queries, search, D2H of scores/ids, verdict check inside)
-            return store.search_host(queries_np, k)
-        qd = queries_host.to(dev, non_blocking=True)
-        s, i = sh.search(qd, k)                         # the public, checked call (status sync, retries)
-        out_host_s.copy_(s, non_blocking=True)
-        out_host_i.copy_(i, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-
-    def timed(fn, steps):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            res = fn()
-        e1.record()
-        barrier()
-        return max_over_ranks(e0.elapsed_time(e1)), res
-
-    for _ in range(args.warmup):
-        step_device()
-    torch.cuda.synchronize()
-    status = L.dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
-    assert status == 0, f"warm-up search incomplete: {L.dab_last_error()}"
-
+    # ------------------------------------------------------------------ the headline store
+    run = SearchRun(env, w, exchange=args.exchange, path=args.path)
+    run.build(keep_cpu_sample=(rank == 0 and world == 1 and not args.no_cpu_baseline))
+    Q, k = w["Q"], w["k"]
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    launches0 = L.dab_launch_count()
-    ms_total, (res_s, res_i) = timed(step_device, args.steps)
-    launches = L.dab_launch_count() - launches0
-    status = L.dab_store_search_status(store._h, torch.cuda.current_stream().cuda_stream)
-    assert status == 0, f"timed search incomplete: {L.dab_last_error()}"
-    for _ in range(args.warmup):          # the host-buffer path has its own first-call costs (pinned copies, lazy loads)
-        step_e2e()
-    ms_e2e, _ = timed(step_e2e, args.steps)
+    head = run.measure(Q, args.steps, args.warmup, verify=False)
     clocks = sampler.stop() if rank == 0 else None
-
-    # roofline pass: the scan kernel bracketed by events on its own stream
-    store.set_profile(True)
-    barrier()
-    for _ in range(args.steps):
-        step_device()
-    prof = store.get_profile()
-    store.set_profile(False)
-    scan_ms = max_over_ranks(prof["scan_ms"]) / args.steps            # per search, slowest rank
-    search_ms = max_over_ranks(prof["search_ms"]) / args.steps
-    elem = 2 if w["dtype"] == "bf16" else 4
-    n_local = hi - lo
-    alg_bytes = n_local * (D * elem + 4) + Q * D * 4 + Q * k * 12       # SURVEY 8(d), per GPU per query batch
-    alg_flops = 2.0 * Q * n_local * D
-    t_hbm, t_tf = alg_bytes / (peaks["hbm"] * 1e9), alg_flops / (peaks["tf"] * 1e12)
-    if t_tf > t_hbm and w["dtype"] == "bf16":
-        roof = dict(bound="tensor", achieved=alg_flops / (scan_ms * 1e-3) / 1e12, peak=peaks["tf"], unit="TFLOP/s")
-        roof["hbm_frac"] = alg_bytes / (scan_ms * 1e-3) / 1e9 / peaks["hbm"]
-    else:
-        roof = dict(bound="hbm", achieved=alg_bytes / (scan_ms * 1e-3) / 1e9, peak=peaks["hbm"], unit="GB/s")
-    roof["frac"] = roof["achieved"] / roof["peak"]
-    roof["kernel"] = "scan (all level launches of one search)"
-    roof["scan_ms_per_search"] = scan_ms
-    roof["search_ms_per_search"] = search_ms
-    roof["scan_launches_per_search"] = prof["scan_launches"] / max(1, args.steps)
-    roof["peak_source"] = peaks["source"]
-    if roof["bound"] == "hbm":
-        roof["peak_note"] = "the HBM peak is the driver's COPY measurement (read + write); a read-only scan can run a few per cent above it"
-    else:
-        roof["peak_note"] = ("the tensor peak is cuBLAS bf16 under the sustained power cap; this kernel also streams the whole shard "
-                             "from HBM and runs power-capped (see clocks.reasons)")
-    roof["traffic"] = None
+    roof = run.roofline(head)
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         roof["traffic"] = json.load(open(tpath)).get(args.workload)
-
-    # correctness guard: device fp32 oracle on a few queries over the whole shard (not timed)
+    if with_targets:
+        # north_star: "top-100 ... at >= 80 % of aggregate HBM roofline for Q <= 64" - the same store, the first 64
+        # queries and the first query alone (the reference's own traffic is single-query: steps/embeddings.py:30,47)
+        for name, q in (("q64", 64), ("q1", 1)):
+            if q < Q:
+                m = run.measure(q, args.steps, args.warmup, verify=False)
+                m["verified"] = None
+                targets[name] = m
+    # correctness guard (not timed): one oracle pass over the corpus serves every query count measured on it
     verified = None
-    if not args.no_verify:
-        verified = verify(torch, ops, store, res_s, res_i, queries_dev, w, lo, hi, N, dev, world, dist)
+    if verify:
+        # EVERY query of the last timed search of each query count is checked
+        verified = run.verify(*head["_res"], Q)
+        for name in ("q64", "q1"):
+            if name in targets:
+                targets[name]["verified"] = run.verify(*targets[name]["_res"], targets[name]["Q"])
+    for name in ("q64", "q1"):
+        if name in targets:
+            targets[name] = dict(run.target(targets[name]), desc=f"{w['desc']} - first {targets[name]['Q']} quer"
+                                 f"{'y' if targets[name]['Q'] == 1 else 'ies'} of the batch (north_star target shape)")
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    value = Q * args.steps / (ms_total * 1e-3)
-    e2e_val = Q * args.steps / (ms_e2e * 1e-3)
-    kernel_path = store.describe_plan(Q, k)["path"]          # what the library actually ran
-    tensor = kernel_path != "simt"
-    line = dict(metric="exact cosine top-k queries/sec", value=value, unit="queries/s", n_gpus=world, steps=args.steps,
-                warmup=args.warmup, ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="strong",
+    tensor = head["kernel_path"] != "simt"
+    arithmetic = ("bf16 x bf16 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
+                  if w["dtype"] == "bf16" and tensor else
+                  "tf32 x tf32 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
+                  if tensor else "fp32 FMA dot products")
+    line = dict(metric="exact cosine top-k queries/sec", value=head["value"], unit="queries/s", n_gpus=world, steps=args.steps,
+                warmup=args.warmup, ms_per_step=head["ms_per_step"], higher_is_better=True, scaling="strong",
                 vs_baseline=None, dtype=("bf16" if w["dtype"] == "bf16" else "tf32") if tensor else "f32", data="synthetic",
-                config={"workload": args.workload, "desc": w["desc"], "rows": N, "rows_per_gpu": n_local, "dim": D,
-                        "store_dtype": w["dtype"], "Q": Q, "k": k, "path": args.path, "kernel_path": kernel_path, "exchange": exchange,
-                        "arithmetic": ("bf16 x bf16 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
-                                       if w["dtype"] == "bf16" and tensor else
-                                       "tf32 x tf32 -> fp32 tcgen05 scan, then fp32 CUDA-core rescoring of the kept candidates"
-                                       if tensor else "fp32 FMA dot products"),
-                        "l2": "inputs larger than L2: every step streams the whole shard "
-                              f"({n_local * D * elem / 1e9:.2f} GB >> 126 MB L2)"},
-                e2e=dict(value=e2e_val, unit="queries/s", h2d_bytes_per_step=Q * D * 4, d2h_bytes_per_step=Q * k * 12,
-                         ms_per_step=ms_e2e / args.steps),
-                gpu_launches=int(launches), clocks=clocks, roofline=roof, verified=verified)
-    if world == 1 and not args.no_cpu_baseline and sample_host is not None:
+                config=search_config(args, w, w["rows"] // world),
+                engine=dict(path=args.path, kernel_path=head["kernel_path"], exchange=run.exchange, arithmetic=arithmetic),
+                e2e=head["e2e"], gpu_launches=head["launches"], clocks=clocks, roofline=roof, verified=verified)
+    if targets:
+        line["targets"] = targets
+    if world == 1 and not args.no_cpu_baseline and run.sample_host is not None:
         from oracle import c_oracle
         c_oracle.build()
         threads = os.cpu_count() or 1
-        v, desc = cpu_search_sample(w, sample_host, queries_host.numpy(), 12.0, threads)
+        v, desc = cpu_search_sample(w, run.sample_host, run.queries_host.numpy(), 12.0, threads)
         line["cpu_baseline"] = dict(value=v, unit="queries/s", cores=threads, kind="port", sample=desc)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
-
-
-def verify(torch, ops, store, res_s, res_i, queries_dev, w, lo, hi, N, dev, world, dist):
-    """Regenerates the shard block by block and ranks the first queries with a plain fp32 torch
-    matmul (TF32 off); the bench's last result must match under the parity bar."""
-    torch.backends.cuda.matmul.allow_tf32 = False
-    nq = min(4, w["Q"])
-    k = w["k"]
-    q = queries_dev[:nq]
-    sdtype = torch.bfloat16 if w["dtype"] == "bf16" else torch.float32
-    best_s = torch.full((nq, k), float("-inf"), device=dev)
-    best_i = torch.full((nq, k), -1, dtype=torch.int64, device=dev)
-    r = lo
-    while r < hi:
-        b = r // BLOCK_ROWS
-        b0 = b * BLOCK_ROWS
-        blk = gen_block(torch, b, min(BLOCK_ROWS, N - b0), w["dim"], dev)
-        part = blk[r - b0: min(hi, b0 + BLOCK_ROWS) - b0].to(sdtype).float()
-        sc = (q @ part.T) / part.norm(dim=1)[None, :]
-        ids = torch.arange(r, r + part.shape[0], device=dev)[None, :].expand(nq, -1)
-        cs, ci = torch.cat([best_s, sc], 1), torch.cat([best_i, ids], 1)
-        top = torch.topk(cs, k, dim=1)
-        best_s, best_i = top.values, torch.gather(ci, 1, top.indices)
-        r += part.shape[0]
-    if world > 1:
-        gs = torch.empty(world, nq, k, device=dev)
-        gi = torch.empty(world, nq, k, dtype=torch.int64, device=dev)
-        dist.all_gather_into_tensor(gs, best_s.contiguous())
-        dist.all_gather_into_tensor(gi, best_i.contiguous())
-        cs, ci = gs.permute(1, 0, 2).reshape(nq, -1), gi.permute(1, 0, 2).reshape(nq, -1)
-        top = torch.topk(cs, k, dim=1)
-        best_s, best_i = top.values, torch.gather(ci, 1, top.indices)
-    got_s, got_i = res_s[:nq], res_i[:nq]
-    bad = 0
-    for qi in range(nq):
-        for j in range(k):
-            if got_i[qi, j] != best_i[qi, j]:
-                # allowed only for near-ties (< 1e-6)
-                alt = (best_i[qi] == got_i[qi, j]).nonzero()
-                other = float(best_s[qi, alt[0, 0]]) if alt.numel() else float(got_s[qi, j])
-                if abs(other - float(best_s[qi, j])) >= 1e-6:
-                    bad += 1
-        if not torch.allclose(got_s[qi], best_s[qi], rtol=1e-5, atol=1e-5):
-            bad += 1
-    assert bad == 0, f"bench result disagrees with the device fp32 oracle in {bad} place(s)"
-    return f"top-{k} of {nq} queries identical to a torch fp32 matmul ranking over all {N} rows"
 
 
 def bench_pool(args, w, rank, world, dev, peaks, barrier, max_over_ranks):

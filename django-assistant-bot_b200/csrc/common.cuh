@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
 #include <string>
 
 #include "../../include/dab_b200.h"
@@ -31,6 +32,33 @@ void count_launch();
         ::dab::count_launch();               \
         DAB_CUDA_OK(cudaGetLastError());     \
     } while (0)
+
+// Tuning switches (environment variables) exist only in builds made with -DDAB_TUNING (tools/); the product
+// library reads no environment variable: the compiler sees a constant nullptr and drops the branches.
+#ifdef DAB_TUNING
+#include <stdlib.h>
+static inline const char *tuning_env(const char *name) { return getenv(name); }
+#else
+static inline const char *tuning_env(const char *) { return nullptr; }
+#endif
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize, raised once per (kernel, device) to the largest size asked so far.
+struct SmemAttrOnce {
+    int set[64] = {};
+    std::mutex mu;
+    template <typename K>
+    cudaError_t ensure(K kernel, int bytes) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev < 0 || dev >= 64) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        std::lock_guard<std::mutex> g(mu);
+        if (set[dev] >= bytes) return cudaSuccess;
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) set[dev] = bytes;
+        return e;
+    }
+};
 
 static inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

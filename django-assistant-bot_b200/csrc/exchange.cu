@@ -185,8 +185,8 @@ extern "C" DAB_API int dab_exchange_merge_topk(void *const *peer_bases_dev, int 
     int P = 32;
     while (P < R * k) P <<= 1;
     const int smem = P * (int)(sizeof(uint32_t) + sizeof(int64_t));
-    DAB_CUDA_OK(cudaFuncSetAttribute(exchange_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kMaxItems * (int)(sizeof(uint32_t) + sizeof(int64_t))));
+    static SmemAttrOnce attr_once;
+    DAB_CUDA_OK(attr_once.ensure(exchange_merge_kernel, kMaxItems * (int)(sizeof(uint32_t) + sizeof(int64_t))));
     exchange_merge_kernel<<<Q, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<unsigned char *const *>(peer_bases_dev), rank, R, max_q, max_k, Q, k, epoch, local_status_dev_or_null,
         out_scores_dev, out_ids_dev, out_status_dev_or_null);

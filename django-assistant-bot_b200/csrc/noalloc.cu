@@ -21,6 +21,10 @@
 //     control block it is going to read, and nothing else is read before it is written.  Two
 //     calls that overlap ON THE GPU (different streams, or different threads/processes' streams
 //     on one device) corrupt each other's candidates: serialise them (one stream, or events).
+//     A call is a SEQUENCE of launches (begin, then scan + compact per round, then finish); a per-device
+//     host mutex is held while that sequence is enqueued, so two host threads that share a stream cannot
+//     interleave their launches.  The mutex orders the enqueue only - it does not wait for the GPU - so
+//     threads using DIFFERENT streams still have to order those streams themselves.
 //   * the first call on each device looks up the array's device address
 //     (cudaGetSymbolAddress) and the SM count.  Make that first call outside any stream capture.
 //
@@ -56,6 +60,7 @@ static_assert(kScratchBytes <= DAB_NOALLOC_SCRATCH_BYTES, "header states a small
 static __device__ __align__(256) unsigned char g_noalloc_scratch[DAB_NOALLOC_SCRATCH_BYTES];
 
 struct DeviceSetup {
+    std::mutex enqueue_mu;   // one call at a time enqueues its launches on this device (host side; see below)
     bool ready = false;
     unsigned char *scratch = nullptr;  // device address of g_noalloc_scratch on this device
     int num_sms = 0;
@@ -105,7 +110,7 @@ extern "C" DAB_API int dab_search_noalloc(const void *rows_dev, int rows_dtype, 
     if (Q > kMaxQ)
         return fail(DAB_E_CAPACITY, "dab_search_noalloc: " + std::to_string(Q) + " queries exceed DAB_NOALLOC_MAX_QUERIES (" +
                                         std::to_string(kMaxQ) + "); split the batch or use a dab_store");
-    if (n_rows < 0 || n_rows >= (int64_t)0xffffffffll) return fail(DAB_E_INVALID, "dab_search_noalloc: n_rows must be in 0..2^32-2");
+    if (n_rows < 0 || n_rows > (int64_t)0x7fffffffll) return fail(DAB_E_INVALID, "dab_search_noalloc: n_rows must be in 0..2^31-1");
     if (Q == 0) return DAB_OK;
     if (!q_dev || !out_scores_dev || !out_ids_dev) return fail(DAB_E_INVALID, "dab_search_noalloc: NULL query/output pointer");
     if (n_rows > 0 && (!rows_dev || !inv_norm_dev)) return fail(DAB_E_INVALID, "dab_search_noalloc: NULL rows/inv_norm pointer");
@@ -115,6 +120,7 @@ extern "C" DAB_API int dab_search_noalloc(const void *rows_dev, int rows_dtype, 
     DeviceSetup *d = nullptr;
     if (int rc = setup_current_device(&d)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    std::lock_guard<std::mutex> enqueue_guard(d->enqueue_mu);   // host threads enqueue whole calls, never interleaved launches
     if (n_rows == 0) return launch_fill_empty(out_scores_dev, out_ids_dev, (int64_t)Q * k, st);
 
     SearchScratch sc{};

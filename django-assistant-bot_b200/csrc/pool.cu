@@ -245,7 +245,7 @@ int launch_pool(const void *hidden, const void *mask, int mask_dtype, float *out
 
 // chosen so B*S gives every SM several CTAs, never dealing fewer than ~16 tokens to a row group
 int pool_pick_splits(int64_t B, int64_t T, int row_groups) {
-    if (const char *e = getenv("DAB_POOL_SPLITS")) {  // tuning aid: force the cluster size (1, 2, 4, 8)
+    if (const char *e = tuning_env("DAB_POOL_SPLITS")) {  // tuning aid: force the cluster size (1, 2, 4, 8)
         const int v = atoi(e);
         if (v == 1 || v == 2 || v == 4 || v == 8) return v;
     }

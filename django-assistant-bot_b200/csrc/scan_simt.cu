@@ -187,7 +187,8 @@ int launch_one(const StoreView &sv, const uint32_t *allow, const SearchScratch &
     auto kern = scan_simt_kernel<BF16, QB, NCH>;
     const int row_bytes = sv.dim * (BF16 ? 2 : 4);
     const size_t smem = simt_smem_bytes(plan.tile_rows, row_bytes);
-    DAB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static SmemAttrOnce attr_once;   // one per template instance
+    DAB_CUDA_OK(attr_once.ensure(kern, (int)smem));
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);

@@ -225,8 +225,6 @@ int umma_queries_per_pass(int dim, int dtype) {
     return best;
 }
 
-void umma_release_maps(void *) {}
-
 int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq, const LevelPlan &plan,
                      int num_sms, cudaStream_t st) {
     if (!umma_supported(sv.dim, sv.dtype))
@@ -246,12 +244,13 @@ int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScr
     if (!plan_umma(sv.dim, per_slice, eb, &up) || groups > num_sms)
         return fail(DAB_E_INVALID, "scan_umma: query block does not fit shared memory");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
-    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
+    if (int rc = cached_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
     const void *qbase = f32 ? static_cast<const void *>(sc.qhat + (size_t)q0 * sv.dim)
                             : static_cast<const void *>(sc.qsplit + (size_t)q0 * sv.dim);
-    if (int rc = make_map(&tmap_q, qbase, (uint64_t)q_rows, (uint64_t)sv.dim, (uint32_t)up.n_pad, f32)) return rc;
+    if (int rc = cached_map(&tmap_q, qbase, (uint64_t)q_rows, (uint64_t)sv.dim, (uint32_t)up.n_pad, f32)) return rc;
     auto kernel = f32 ? scan_umma_kernel<true> : scan_umma_kernel<false>;
-    DAB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)up.smem));
+    static SmemAttrOnce attr_once[2];
+    DAB_CUDA_OK(attr_once[f32 ? 1 : 0].ensure(kernel, (int)up.smem));
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long seqs = max_tiles < num_sms / groups ? max_tiles : num_sms / groups;

@@ -130,9 +130,6 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 const long long t = level_tile(plan, lvl, pair_id + it * num_pairs);
                 const int row0 = (int)(t * kStepRows) + (int)rank * kHalfRows;
                 for (int st = 0; st < stages_per_step; st++) {
-#ifdef DAB_EXP_NOLOAD
-                    if (st >= 0) continue;
-#endif
                     mbar_wait_bounded(&empty[s], ph ^ 1u);
                     unsigned char *dst = b_smem + (size_t)s * kStageBytes;
 #pragma unroll
@@ -150,32 +147,15 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             tc_fence_after();
             int s = 0;
             uint32_t ph = 0;
-#ifdef DAB_EXP_TIMING
-            long long tm_tmem = 0, tm_full = 0, tm_start = clock64();
-#endif
             for (long long it = 0; it < my_steps; it++) {
                 const int a = (int)(it & 1);
                 const uint32_t aph = (uint32_t)((it >> 1) & 1);
-#ifdef DAB_EXP_TIMING
-                long long t0_ = clock64();
-#endif
                 mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);
-#ifdef DAB_EXP_TIMING
-                tm_tmem += clock64() - t0_;
-#endif
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_acc0 + (uint32_t)(a * kAccCols);
                 for (int st = 0; st < stages_per_step; st++) {
-#ifndef DAB_EXP_NOLOAD
                     mbar_arrive_expect_tx(&full[s], 2 * kStageBytes);      // my half + my peer's half
-#ifdef DAB_EXP_TIMING
-                    long long t1_ = clock64();
-#endif
                     mbar_wait_bounded(&full[s], ph);
-#ifdef DAB_EXP_TIMING
-                    tm_full += clock64() - t1_;
-#endif
-#endif
                     tc_fence_after();
                     const uint32_t sbase = smem_u32(b_smem + (size_t)s * kStageBytes);
 #pragma unroll
@@ -194,10 +174,6 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 }
                 umma_commit_mc2(&tmem_full[a], (uint16_t)0x3u);
             }
-#ifdef DAB_EXP_TIMING
-            if (blockIdx.x == 0)
-                printf("[lvl %d] qa issuer: steps %lld total %lld wait_tmem_empty %lld wait_full %lld\n", lvl, my_steps, clock64() - tm_start, tm_tmem, tm_full);
-#endif
         }
     } else if (warp == 3) {
         // ------------------------------------------------------------ flusher: staged candidates -> global buffers
@@ -243,9 +219,6 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             const float x = r < sv.n ? sv.inv_norm[r] : 0.f;
             s_inv[et] = x > 0.f ? x : __int_as_float(0x7fc00000);   // zero rows / rows past the end: NaN, never >= tau
         }
-#ifdef DAB_EXP_TIMING
-        long long te_pend = 0, te_full = 0, te_start = clock64();
-#endif
         for (long long it = 0; it < my_steps; it++) {
             const int a = (int)(it & 1);
             const uint32_t aph = (uint32_t)((it >> 1) & 1);
@@ -256,19 +229,9 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 const float x = r < sv.n ? sv.inv_norm[r] : 0.f;
                 inv_next = x > 0.f ? x : __int_as_float(0x7fc00000);
             }
-#ifdef DAB_EXP_TIMING
-            long long t3_ = clock64();
-#endif
             named_bar_sync(1, 128);                             // s_inv[a] written by all epilogue threads
             mbar_wait_bounded(&pend_free[a], aph ^ 1u);
-#ifdef DAB_EXP_TIMING
-            long long t4_ = clock64();
-            te_pend += t4_ - t3_;
-#endif
             mbar_wait_bounded(&tmem_full[a], aph);
-#ifdef DAB_EXP_TIMING
-            te_full += clock64() - t4_;
-#endif
             tc_fence_after();
             const uint32_t taddr = tmem_acc0 + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * kAccCols);
             const float *inv = s_inv + a * kStepRows;
@@ -277,7 +240,6 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
             const uint32_t lt = (1u << lane) - 1u;
             uint64_t *wkey = pend_key + a * kPendCap + wq * kWarpCap;
             uint32_t *wq_ = pend_q + a * kPendCap + wq * kWarpCap;
-#ifndef DAB_EXP_NOEPI
             tmem_ld16(taddr, v0);
 #pragma unroll
             for (int c0 = 0; c0 < kStepRows; c0 += 32) {
@@ -320,7 +282,6 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                     }
                 }
             }
-#endif
             tc_fence_before();
             if (et < kStepRows) s_inv[(a ^ 1) * kStepRows + et] = inv_next;   // for the next step (other stage)
             __syncwarp();
@@ -330,10 +291,6 @@ scan_umma_qa_kernel(const __grid_constant__ CUtensorMap tmap_rows, StoreView sv,
                 mbar_arrive(&pend_full[a]);
             }
         }
-#ifdef DAB_EXP_TIMING
-        if (blockIdx.x == 0 && tid == 128)
-            printf("[lvl %d] qa epilogue w4: total %lld wait_bar+pend_free %lld wait_tmem_full %lld\n", lvl, clock64() - te_start, te_pend, te_full);
-#endif
     }
     // ---------------------------------------------------------------- teardown
     tc_fence_before();
@@ -374,8 +331,10 @@ int launch_scan_umma_qa(const StoreView &sv, const uint32_t *allow, const Search
         return fail(DAB_E_INVALID, "scan_umma_qa: needs a bf16 store, dim % 128 == 0, dim <= 768 and <= 256 queries");
     if (plan.tile_rows != kStepRows) return fail(DAB_E_INVALID, "scan_umma_qa: level plan built for another tile size");
     alignas(64) CUtensorMap tmap_rows;
-    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kHalfRows)) return rc;
-    DAB_CUDA_OK(cudaFuncSetAttribute(scan_umma_qa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qp.smem));
+    if (int rc = cached_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kHalfRows)) return rc;
+    static SmemAttrOnce attr_once;
+    static ClusterOccupancyCache occ_cache;
+    DAB_CUDA_OK(attr_once.ensure(scan_umma_qa_kernel, (int)qp.smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(num_sms / 2 * 2), 1, 1);
     cfg.blockDim = dim3(kThreads, 1, 1);
@@ -389,13 +348,13 @@ int launch_scan_umma_qa(const StoreView &sv, const uint32_t *allow, const Search
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     int max_clusters = 0;
-    DAB_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_clusters, scan_umma_qa_kernel, &cfg));
+    DAB_CUDA_OK(occ_cache.get(&max_clusters, scan_umma_qa_kernel, &cfg, 2));
     if (max_clusters < 1) return fail(DAB_E_CUDA, "scan_umma_qa: no CTA pair fits on this device");
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long pairs = max_tiles < max_clusters ? max_tiles : max_clusters;
     cfg.gridDim = dim3((unsigned)(pairs * 2), 1, 1);
-    static const bool debug = getenv("DAB_DEBUG") != nullptr;
+    static const bool debug = tuning_env("DAB_DEBUG") != nullptr;
     if (debug) fprintf(stderr, "[dab] qa: nq=%d stages=%d smem=%zu pairs=%lld levels=%d\n", nq, qp.stages, qp.smem, pairs, plan.num_levels);
     DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, scan_umma_qa_kernel, tmap_rows, sv, allow, sc, q0, nq, qp.stages, plan));
     count_launch();

@@ -24,8 +24,7 @@
 //                              flushes the epilogue warps' staged candidates to the global buffers
 //   warps 4-11                 epilogue: two warps per TMEM lane quarter, half of the pair's columns each
 // The single-lane roles are entered through elect_one() and every tcgen05/TMA operand is warp-uniform
-// (umma.cuh explains what it costs otherwise).  -DDAB_EXP_* macros build timing/ablation variants of this
-// file for tools/exp_scan.py; none is defined in the product build.
+// (umma.cuh explains what it costs otherwise).
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -129,23 +128,11 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                 const uint16_t mask = (uint16_t)((1u << rank) | (num_pairs == 2 ? (1u << (rank + 2)) : 0u));
                 int s = 0;
                 uint32_t ph = 0;
-#ifdef DAB_EXP_TIMING
-                long long tm_empty = 0, tm_pstart = clock64();
-#endif
                 for (long long it = 0; it < my_tiles; it++) {
                     const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
                     const int row0 = (int)(t * kSuperRows) + half * kTileRows;
                     for (int kb = 0; kb < num_kb; kb++) {
-#ifdef DAB_EXP_NOLOAD
-                        if (kb >= 0) continue;
-#endif
-#ifdef DAB_EXP_TIMING
-                        long long t2_ = clock64();
-#endif
                         mbar_wait_bounded(&empty[s], ph ^ 1u);
-#ifdef DAB_EXP_TIMING
-                        tm_empty += clock64() - t2_;
-#endif
 
                         if (num_pairs == 2)
                             tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s], mask);
@@ -154,9 +141,6 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                         if (++s == stages) { s = 0; ph ^= 1u; }
                     }
                 }
-#ifdef DAB_EXP_TIMING
-                if (blockIdx.x == 0) printf("[lvl %d cta 0] producer: total %lld wait_empty %lld\n", lvl, clock64() - tm_pstart, tm_empty);
-#endif
             }
         }
     } else if (warp == 1) {
@@ -168,62 +152,30 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             tc_fence_after();
             int s = 0;
             uint32_t ph = 0;
-#ifdef DAB_EXP_TIMING
-            long long tm_tmem = 0, tm_full = 0, tm_start = clock64();
-#endif
             for (long long it = 0; it < my_tiles; it++) {
                 const int a = (int)(it % acc_stages);
                 const uint32_t aph = (uint32_t)((it / acc_stages) & 1);
-#ifdef DAB_EXP_TIMING
-                long long t0_ = clock64();
-#endif
                 mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);
-#ifdef DAB_EXP_TIMING
-                tm_tmem += clock64() - t0_;
-#endif
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(a * n_pair);
                 for (int kb = 0; kb < num_kb; kb++) {
                     // both 16 KiB halves of the stage (mine and my peer's) report to this barrier
-#ifndef DAB_EXP_NOLOAD
                     mbar_arrive_expect_tx(&full[s], 2 * kAStageBytes);
-#endif
-#ifdef DAB_EXP_TIMING
-                    long long t1_ = clock64();
-#endif
-#ifndef DAB_EXP_NOLOAD
                     mbar_wait_bounded(&full[s], ph);
-#endif
-#ifdef DAB_EXP_TIMING
-                    tm_full += clock64() - t1_;
-#endif
-#ifndef DAB_EXP_NOKBFENCE
                     tc_fence_after();
-#endif
                     const uint64_t da = make_smem_desc(smem_u32(a_smem + (size_t)s * kAStageBytes));
                     const uint64_t db = make_smem_desc(smem_u32(b_smem + (size_t)kb * b_kb_bytes));
-#ifndef DAB_EXP_MMAS
-#define DAB_EXP_MMAS (kBlockK / kUmmaK)
-#endif
 #pragma unroll
-                    for (int k = 0; k < DAB_EXP_MMAS; k++)
+                    for (int k = 0; k < (kBlockK / kUmmaK); k++)
                         if constexpr (F32)
                             umma_tf32_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
                         else
                             umma_f16_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
-#ifdef DAB_EXP_COMMIT_EVERY
-                    if (kb % DAB_EXP_COMMIT_EVERY == DAB_EXP_COMMIT_EVERY - 1)
-#endif
                     umma_commit_mc2(&empty[s], (uint16_t)0x3u);        // the loaders are ranks 0 and 1
                     if (++s == stages) { s = 0; ph ^= 1u; }
                 }
                 umma_commit_mc2(&tmem_full[a], pair_mask);
             }
-#ifdef DAB_EXP_TIMING
-            if (blockIdx.x == 0 || blockIdx.x == 2)
-                printf("[lvl %d cta %d] issuer: tiles %lld total %lld wait_tmem_empty %lld wait_full %lld\n", lvl, (int)blockIdx.x, my_tiles,
-                       clock64() - tm_start, tm_tmem, tm_full);
-#endif
         }
     } else if (warp == 3) {
         if (lane == 0) {
@@ -255,9 +207,6 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         };
         long long row = row_of(0);
         float rinv = row < sv.n ? sv.inv_norm[row] : 0.f;
-#ifdef DAB_EXP_TIMING
-        long long te_pend = 0, te_full = 0, te_start = clock64();
-#endif
         for (long long it = 0; it < my_tiles; it++) {
             const int a = (int)(it % acc_stages);                  // accumulator stage
             const uint32_t aph = (uint32_t)((it / acc_stages) & 1);
@@ -265,26 +214,14 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             const uint32_t plph = (uint32_t)((it >> 1) & 1);
             const long long row_next = it + 1 < my_tiles ? row_of(it + 1) : sv.n;
             const float rinv_next = row_next < sv.n ? sv.inv_norm[row_next] : 0.f;
-#ifdef DAB_EXP_TIMING
-            long long t3_ = clock64();
-#endif
             mbar_wait_bounded(&pend_free[pl], plph ^ 1u);     // the flusher is done with this list (tile it-2)
-#ifdef DAB_EXP_TIMING
-            long long t4_ = clock64();
-            te_pend += t4_ - t3_;
-#endif
             mbar_wait_bounded(&tmem_full[a], aph);
-#ifdef DAB_EXP_TIMING
-            te_full += clock64() - t4_;
-#endif
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair + c_begin);
             const int ew = warp - 4;                                // 0..7
             const WarpList wl = {pend_key + pl * kPendCap + ew * kWarpCap, pend_q + pl * kPendCap + ew * kWarpCap, kWarpCap};
             uint32_t hits = 0;
-#ifndef DAB_EXP_NOEPI
             hits = epilogue_tile_wl(taddr, c_count, rinv, row, tau_s + c_begin, q0 + c_begin, allow, sc, wl);
-#endif
             row = row_next;
             rinv = rinv_next;
             tc_fence_before();
@@ -295,11 +232,6 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                 mbar_arrive(&pend_full[pl]);                        // release: the flusher sees the list and its count
             }
         }
-#ifdef DAB_EXP_TIMING
-        if (blockIdx.x < 2 && lane == 0 && warp == 4)
-            printf("[lvl %d cta %d] epilogue w4: total %lld wait_pend_free %lld wait_tmem_full %lld\n", lvl, (int)blockIdx.x,
-                   clock64() - te_start, te_pend, te_full);
-#endif
     }
     // ---------------------------------------------------------------- teardown
     tc_fence_before();
@@ -379,14 +311,16 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
         return fail(DAB_E_INVALID, "scan_umma_quad: needs a bf16 or fp32 store and a query block that fits shared memory");
     if (plan.tile_rows != kSuperRows) return fail(DAB_E_INVALID, "scan_umma_quad: level plan built for another tile size");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
-    if (int rc = make_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
+    if (int rc = cached_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
     // B = the unit-norm fp32 queries (fp32 stores) or their bf16 copy (bf16 stores); rows past the buffer read as zero
     const void *qbase = f32 ? static_cast<const void *>(sc.qhat + (size_t)q0 * sv.dim)
                             : static_cast<const void *>(sc.qsplit + (size_t)q0 * sv.dim);
     const uint64_t q_rows = (uint64_t)((f32 ? DAB_MAX_QUERY_BATCH : 2 * DAB_MAX_QUERY_BATCH) - q0);
-    if (int rc = make_map(&tmap_q, qbase, q_rows, (uint64_t)sv.dim, (uint32_t)(qp.n_pair / 2), f32)) return rc;
+    if (int rc = cached_map(&tmap_q, qbase, q_rows, (uint64_t)sv.dim, (uint32_t)(qp.n_pair / 2), f32)) return rc;
     auto kernel = f32 ? scan_umma_quad_kernel<true> : scan_umma_quad_kernel<false>;
-    DAB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qp.smem));
+    static SmemAttrOnce attr_once[2];
+    static ClusterOccupancyCache occ_cache[2];
+    DAB_CUDA_OK(attr_once[f32 ? 1 : 0].ensure(kernel, (int)qp.smem));
     // how many 4-CTA clusters can be resident at once (GPC shapes strand a few SMs)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(num_sms / kCluster * kCluster), 1, 1);
@@ -401,16 +335,16 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     int max_clusters = 0;
-    DAB_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_clusters, kernel, &cfg));
+    DAB_CUDA_OK(occ_cache[f32 ? 1 : 0].get(&max_clusters, kernel, &cfg, kCluster));
     if (max_clusters < 1) return fail(DAB_E_CUDA, "scan_umma_quad: no 4-CTA cluster fits on this device");
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long clusters = max_tiles < max_clusters ? max_tiles : max_clusters;
     int acc = qp.tmem_cols / qp.n_pair;
     if (acc > kMaxAcc) acc = kMaxAcc;
-    if (const char *e = getenv("DAB_QUAD_ACC")) acc = atoi(e) >= 2 && atoi(e) <= acc ? atoi(e) : acc;  // tuning aid
-    if (const char *e = getenv("DAB_QUAD_STAGES")) qp.stages = atoi(e) >= 2 && atoi(e) <= qp.stages ? atoi(e) : qp.stages;
-    static const bool debug = getenv("DAB_DEBUG") != nullptr;
+    if (const char *e = tuning_env("DAB_QUAD_ACC")) acc = atoi(e) >= 2 && atoi(e) <= acc ? atoi(e) : acc;  // tuning aid
+    if (const char *e = tuning_env("DAB_QUAD_STAGES")) qp.stages = atoi(e) >= 2 && atoi(e) <= qp.stages ? atoi(e) : qp.stages;
+    static const bool debug = tuning_env("DAB_DEBUG") != nullptr;
     if (debug)
         fprintf(stderr, "[dab] quad: pairs=%d nq=%d n_pair=%d stages=%d tmem_cols=%d smem=%zu max_clusters=%d clusters=%lld levels=%d\n", num_pairs, nq,
                 qp.n_pair, qp.stages, qp.tmem_cols, qp.smem, max_clusters, clusters, plan.num_levels);

@@ -20,6 +20,12 @@ struct SearchScratch {
     int *overflowed;        // [256] query overflowed in the current round
     int *inexact_q;         // [256] tensor path: more rows inside the margin than kept -> outputs poisoned (may be null)
     SearchCtrl *ctrl;
+    // Per-CALL verdict slots {incomplete, inexact}: the finish kernel of every query chunk copies the sticky flags
+    // there, so the verdict of a search survives the next search's reset of `ctrl` (two threads on one store).
+    // verdict_dev lives in HBM (read by dab_exchange_merge_topk), verdict_host in pinned host memory (read by
+    // dab_store_search_status after a stream synchronise - no copy).  Either may be null.
+    int *verdict_dev;
+    int *verdict_host;
 };
 
 size_t search_scratch_bytes(int dim);

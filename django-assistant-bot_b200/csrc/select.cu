@@ -44,6 +44,8 @@ SearchScratch carve_scratch(void *base, int dim) {
     s.inexact_q = reinterpret_cast<int *>(p);
     p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
     s.ctrl = reinterpret_cast<SearchCtrl *>(p);
+    s.verdict_dev = nullptr;
+    s.verdict_host = nullptr;
     return s;
 }
 
@@ -377,6 +379,20 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
     }
 }
 
+// the finish kernels' single bookkeeping thread: publish this call's verdict so far (see SearchScratch)
+__device__ __forceinline__ void publish_verdict(const SearchScratch &sc) {
+    const int inc = sc.ctrl->sticky_incomplete, inx = sc.ctrl->sticky_inexact;
+    if (sc.verdict_dev) {
+        sc.verdict_dev[0] = inc;
+        sc.verdict_dev[1] = inx;
+    }
+    if (sc.verdict_host) {
+        sc.verdict_host[0] = inc;
+        sc.verdict_host[1] = inx;
+        __threadfence_system();
+    }
+}
+
 // ---------------------------------------------------------------- finish (exact paths): keys -> outputs
 __global__ void __launch_bounds__(128)
 finish_exact_kernel(SearchScratch sc, StoreView sv, int k, int num_levels, float *__restrict__ out_scores,
@@ -385,7 +401,10 @@ finish_exact_kernel(SearchScratch sc, StoreView sv, int k, int num_levels, float
     const bool done = sc.ctrl->cur_level >= num_levels;
     const int cnt = done ? min((int)sc.cand_count[qi], k) : 0;
     const uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
-    if (qi == 0 && threadIdx.x == 0 && !done) sc.ctrl->sticky_incomplete = 1;
+    if (qi == 0 && threadIdx.x == 0) {
+        if (!done) sc.ctrl->sticky_incomplete = 1;
+        publish_verdict(sc);
+    }
     for (int j = threadIdx.x; j < k; j += blockDim.x) {
         float s;
         int64_t id;
@@ -422,6 +441,7 @@ finish_rescore_kernel(SearchScratch sc, StoreView sv, int k, int k_keep, int num
     if (qi == 0 && tid == 0) {
         if (sc.ctrl->cur_level < num_levels) sc.ctrl->sticky_incomplete = 1;
         if (sc.ctrl->inexact) sc.ctrl->sticky_inexact = 1;
+        publish_verdict(sc);
     }
     int P = 32;
     while (P < cnt) P <<= 1;
@@ -563,7 +583,8 @@ int launch_compact(const SearchScratch &sc, int nq, int k, int num_levels, cudaS
 
 int launch_compact_margin(const SearchScratch &sc, int nq, int k, int k_cap, float margin, int num_levels, cudaStream_t st) {
     const int smem = kCandCap * sizeof(uint64_t);
-    DAB_CUDA_OK(cudaFuncSetAttribute(compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    static SmemAttrOnce attr_once;
+    DAB_CUDA_OK(attr_once.ensure(compact_kernel, smem));
     compact_kernel<<<nq, kCompactThreads, smem, st>>>(sc, nq, k, k_cap, margin, num_levels);
     DAB_LAUNCH_OK();
     return DAB_OK;
@@ -604,8 +625,8 @@ extern "C" DAB_API int dab_merge_topk(const float *gathered_scores, const int64_
     int P = 32;
     while (P < R * k) P <<= 1;
     const int smem = P * (int)(sizeof(uint32_t) + sizeof(int64_t));
-    DAB_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kMergeMax * (int)(sizeof(uint32_t) + sizeof(int64_t))));
+    static SmemAttrOnce attr_once;
+    DAB_CUDA_OK(attr_once.ensure(merge_topk_kernel, kMergeMax * (int)(sizeof(uint32_t) + sizeof(int64_t))));
     merge_topk_kernel<<<Q, kMergeThreads, smem, static_cast<cudaStream_t>(stream)>>>(gathered_scores, gathered_ids, R, Q, k,
                                                                                       out_scores, out_ids);
     DAB_LAUNCH_OK();

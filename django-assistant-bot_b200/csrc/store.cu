@@ -31,7 +31,6 @@ static std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 int simt_queries_per_pass(int dim, int dtype);
-void umma_release_maps(void *maps);
 
 }  // namespace dab
 
@@ -58,10 +57,12 @@ struct dab_store {
     int num_sms = 148;
     int spare_rounds = 0;
     int path = 0;
-    int last_num_levels = 0;
-    void *umma_maps = nullptr;  // tensor maps of the tcgen05 path (built lazily)
     dab_profile prof;
-    dab::SearchCtrl *status_host = nullptr;  // pinned landing buffer of dab_store_search_status
+    // Per-call verdicts: search number `seq` owns slot seq % kVerdictSlots of both rings; its finish kernels write
+    // {incomplete, inexact} there (HBM ring for the exchange kernel, pinned ring for dab_store_search_status).
+    int *verdict_ring_dev = nullptr;
+    int *verdict_ring_host = nullptr;
+    uint64_t search_seq = 0;
     // staging of dab_store_search_host (allocated on first use): pinned host + device buffers for one
     // chunk of DAB_MAX_QUERY_BATCH queries and their DAB_MAX_K results
     void *io_host = nullptr;
@@ -73,7 +74,6 @@ struct dab_store {
     // Auto path, few queries: the tensor pass is the faster choice unless the corpus is so dense around the
     // top-k that the rescoring margin overflows (DAB_E_INEXACT) and the call has to be repeated on the CUDA
     // cores.  After such a verdict the next `small_simt_credit` small searches go to the CUDA cores directly.
-    int last_small_tensor = 0;   // the last search was a small (<= simt queries per pass) auto search on the tensor path
     int small_simt_credit = 0;
     std::mutex mu;
 };
@@ -81,6 +81,18 @@ struct dab_store {
 namespace dab {
 
 namespace {
+
+constexpr int kVerdictSlots = 256;
+
+// What this thread searched last: dab_store_search_status / dab_store_status_dev answer for THAT call, not for
+// whatever another thread enqueued on the same store in between.
+struct LastSearch {
+    const dab_store *store = nullptr;
+    uint64_t seq = 0;
+    bool empty = true;          // nothing was scanned (empty store): the verdict is DAB_OK
+    bool small_tensor = false;  // a small (<= CUDA-core queries per pass) auto search that took the tensor path
+};
+thread_local LastSearch t_last;
 
 // ---------------------------------------------------------------- append: copy/convert rows, 1/|row|
 // One warp per row; 128-bit loads/stores; the norm is taken from the values as STORED.
@@ -166,7 +178,8 @@ extern "C" DAB_API int dab_store_create(dab_store **out, int device, int64_t cap
     if (dim <= 0 || dim % ve) return fail(DAB_E_INVALID, "dab_store_create: dim must be a positive multiple of 4 (fp32) / 8 (bf16)");
     const size_t row_bytes = (size_t)dim * (dtype == DAB_BF16 ? 2 : 4);
     if (row_bytes > DAB_MAX_ROW_BYTES) return fail(DAB_E_INVALID, "dab_store_create: row wider than DAB_MAX_ROW_BYTES");
-    if (capacity_rows <= 0 || capacity_rows >= (int64_t)0xffffffffll) return fail(DAB_E_INVALID, "dab_store_create: capacity must be in 1..2^32-2");
+    // row indices travel as int32 TMA coordinates and as the low 32 bits of a candidate key
+    if (capacity_rows <= 0 || capacity_rows > (int64_t)0x7fffffffll) return fail(DAB_E_INVALID, "dab_store_create: capacity must be in 1..2^31-1");
     DAB_CUDA_OK(cudaSetDevice(device));
     dab_store *s = new (std::nothrow) dab_store();
     if (!s) return fail(DAB_E_INVALID, "dab_store_create: out of host memory");
@@ -192,8 +205,11 @@ extern "C" DAB_API int dab_store_create(dab_store **out, int device, int64_t cap
     int sms = 0;
     if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return bail("attr", e);
     s->num_sms = sms;
-    if ((e = cudaHostAlloc(reinterpret_cast<void **>(&s->status_host), sizeof(SearchCtrl), cudaHostAllocDefault)) != cudaSuccess)
-        return bail("status buffer", e);
+    if ((e = cudaMalloc(&s->verdict_ring_dev, (kVerdictSlots + 1) * 2 * sizeof(int))) != cudaSuccess) return bail("verdict ring", e);
+    if ((e = cudaMemset(s->verdict_ring_dev, 0, (kVerdictSlots + 1) * 2 * sizeof(int))) != cudaSuccess) return bail("memset", e);
+    if ((e = cudaHostAlloc(reinterpret_cast<void **>(&s->verdict_ring_host), (kVerdictSlots + 1) * 2 * sizeof(int), cudaHostAllocMapped)) != cudaSuccess)
+        return bail("verdict ring (pinned)", e);
+    memset(s->verdict_ring_host, 0, (kVerdictSlots + 1) * 2 * sizeof(int));
     *out = s;
     return DAB_OK;
 }
@@ -201,12 +217,12 @@ extern "C" DAB_API int dab_store_create(dab_store **out, int device, int64_t cap
 extern "C" DAB_API void dab_store_destroy(dab_store *s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    if (s->umma_maps) umma_release_maps(s->umma_maps);
     cudaFree(s->rows);
     cudaFree(s->inv_norm);
     cudaFree(s->ids);
     cudaFree(s->scratch_base);
-    if (s->status_host) cudaFreeHost(s->status_host);
+    cudaFree(s->verdict_ring_dev);
+    if (s->verdict_ring_host) cudaFreeHost(s->verdict_ring_host);
     if (s->scratch_free) cudaEventDestroy(s->scratch_free);
     if (s->io_host) cudaFreeHost(s->io_host);
     cudaFree(s->io_dev);
@@ -317,9 +333,9 @@ struct SearchPlan {
     LevelPlan levels;
 };
 
-SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq, int k) {
+SearchPlan choose_plan(const dab_store *s, int path, int64_t n, int dim, int dtype, int nq, int k) {
     SearchPlan sp = {};
-    sp.path = s->path;
+    sp.path = path;
     // auto: the tensor path whenever the row layout allows it - measured faster than the CUDA-core kernel at every
     // query count, 1 included (12.5M x 768 bf16: 2.7 ms vs 3.3 / 6.5 / 9.3 ms at Q = 1 / 2 / 4; fp32 via tf32:
     // 2.5 ms vs 2.8 / 4.1 / 5.7 ms), and no slower on stores of a few thousand rows.  The CUDA-core kernel
@@ -339,9 +355,9 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
         sp.margin = 2.0f * eps;
         sp.k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // wide blocks that do not fit one SM's shared memory go to the 4-CTA cluster kernel
-        static const bool no_quad = getenv("DAB_NO_QUAD") != nullptr;  // tuning aid: use query-slice groups instead
-        // queries-as-A kernel: parity-green but measured slower than the cluster kernel; opt-in
-        static const bool use_qa = getenv("DAB_USE_QA") != nullptr;
+        static const bool no_quad = tuning_env("DAB_NO_QUAD") != nullptr;  // tuning builds only: query-slice groups instead
+        // queries-as-A kernel: parity-green but measured slower than the cluster kernel; tuning builds only
+        static const bool use_qa = tuning_env("DAB_USE_QA") != nullptr;
         const bool wide = nq > umma_queries_per_pass(dim, dtype);
         sp.qa = wide && use_qa && qa_supported(dim, dtype, nq);
         sp.quad = wide && !sp.qa && !no_quad && quad_supported(dim, dtype, nq);
@@ -359,7 +375,7 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
         // Q = 100..128 against 3.6-3.7 ms for the 4-CTA form (whose N = 64 MMAs are issue-bound); two pair passes
         // for Q = 256 cost 6.0 ms against 4.7 ms.  It also beats the single-CTA kernel once that one's epilogue gets
         // long (Q = 80: 2.89 vs 3.00 ms, Q = 96: 2.91 vs 3.25 ms; equal at Q <= 64).  DAB_PAIR_MIN_Q moves the switch.
-        static const int pair_min_q = getenv("DAB_PAIR_MIN_Q") ? atoi(getenv("DAB_PAIR_MIN_Q")) : 65;
+        static const int pair_min_q = tuning_env("DAB_PAIR_MIN_Q") ? atoi(tuning_env("DAB_PAIR_MIN_Q")) : 65;
         if (!sp.qa && !no_quad && nq <= pair_queries_per_pass(dim, dtype) && quad_supported(dim, dtype, nq) &&
             (wide || (dtype == DAB_BF16 && nq >= pair_min_q))) {
             sp.quad = true;
@@ -379,19 +395,18 @@ SearchPlan choose_plan(const dab_store *s, int64_t n, int dim, int dtype, int nq
 }
 
 // The rounds of one query chunk (<= 256 queries), all enqueued on `st` without a host sync.
-int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc, const float *q_dev, int nq, int k,
-                     const uint32_t *allow, float *out_scores, int64_t *out_ids, int *num_levels_out, cudaStream_t st,
+int run_search_chunk(dab_store *s, int path, int spare_rounds, const StoreView &sv, const SearchScratch &sc, const float *q_dev,
+                     int nq, int k, const uint32_t *allow, float *out_scores, int64_t *out_ids, cudaStream_t st,
                      bool first_chunk) {
-    const SearchPlan sp = choose_plan(s, sv.n, sv.dim, sv.dtype, nq, k);
+    const SearchPlan sp = choose_plan(s, path, sv.n, sv.dim, sv.dtype, nq, k);
     const LevelPlan &plan = sp.levels;
-    *num_levels_out = plan.num_levels;
     if (sp.path == 2) {
         if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, sv.dtype == DAB_BF16, st, first_chunk)) return rc;
-        for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
+        for (int r = 0; r < plan.num_levels + spare_rounds; r++) {
             {
                 // one launch scores all nq queries
                 ScanTimer tm(s->prof, st);
-                static const bool pair_mode = getenv("DAB_WIDE_PAIRS") != nullptr;  // tuning aid
+                static const bool pair_mode = tuning_env("DAB_WIDE_PAIRS") != nullptr;  // tuning builds only
                 if (sp.qa) {
                     if (int rc = launch_scan_umma_qa(sv, allow, sc, 0, nq, plan, s->num_sms, st)) return rc;
                 } else if (sp.quad && sp.pairs == 1) {
@@ -417,7 +432,7 @@ int run_search_chunk(dab_store *s, const StoreView &sv, const SearchScratch &sc,
     }
     const int qb = simt_queries_per_pass(sv.dim, sv.dtype);
     if (int rc = launch_search_begin(sc, q_dev, nq, sv.dim, false, st, first_chunk)) return rc;
-    for (int r = 0; r < plan.num_levels + s->spare_rounds; r++) {
+    for (int r = 0; r < plan.num_levels + spare_rounds; r++) {
         for (int q0 = 0; q0 < nq; q0 += qb) {
             const int n_sub = nq - q0 < qb ? nq - q0 : qb;
             ScanTimer tm(s->prof, st);
@@ -441,18 +456,20 @@ int validate_search(const dab_store *s, const float *q_dev, int Q, int k, const 
 
 }  // namespace dab
 
-extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow, float *out_scores,
-                                int64_t *out_ids, void *stream) {
-    if (int rc = check_store(s, "dab_store_search")) return rc;
-    if (int rc = validate_search(s, q_dev, Q, k, out_scores, out_ids)) return rc;
-    if (Q == 0) return DAB_OK;
+namespace dab {
+// One search call: all query chunks enqueued on `st` under the store's mutex.  `path` / `spare_rounds` < 0 = the
+// store's settings.  The call's verdict lands in slot seq % kVerdictSlots of the store's rings.
+static int search_impl(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow, float *out_scores, int64_t *out_ids,
+                       int path, int spare_rounds, cudaStream_t st) {
     std::lock_guard<std::mutex> g(s->mu);
     DAB_CUDA_OK(cudaSetDevice(s->device));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (s->size == 0) {
-        s->last_num_levels = 0;
-        return launch_fill_empty(out_scores, out_ids, (int64_t)Q * k, st);
-    }
+    if (path < 0) path = s->path;
+    if (spare_rounds < 0) spare_rounds = s->spare_rounds;
+    t_last.store = s;
+    t_last.seq = ++s->search_seq;
+    t_last.empty = s->size == 0;
+    t_last.small_tensor = false;
+    if (s->size == 0) return launch_fill_empty(out_scores, out_ids, (int64_t)Q * k, st);
     StoreView sv;
     sv.rows = s->rows;
     sv.inv_norm = s->inv_norm;
@@ -461,10 +478,14 @@ extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q,
     sv.n = s->size;
     sv.dim = s->dim;
     sv.dtype = s->dtype;
+    SearchScratch sc = s->scratch;
+    const int slot = (int)(t_last.seq % kVerdictSlots);
+    sc.verdict_dev = s->verdict_ring_dev + 2 * slot;
+    sc.verdict_host = s->verdict_ring_host + 2 * slot;
     if (!s->scratch_free) DAB_CUDA_OK(cudaEventCreateWithFlags(&s->scratch_free, cudaEventDisableTiming));
     DAB_CUDA_OK(cudaStreamWaitEvent(st, s->scratch_free, 0));   // no-op for the stream that recorded it last
     const bool small = Q <= simt_queries_per_pass(s->dim, s->dtype);
-    s->last_small_tensor = s->path == 0 && small && s->small_simt_credit == 0 && umma_supported(s->dim, s->dtype);
+    t_last.small_tensor = path == 0 && small && s->small_simt_credit == 0 && umma_supported(s->dim, s->dtype);
     ScanTimer whole(s->prof, st, true);
     struct Stop {
         ScanTimer &t;
@@ -472,37 +493,56 @@ extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q,
     } stop_on_exit{whole};
     for (int q0 = 0; q0 < Q; q0 += DAB_MAX_QUERY_BATCH) {
         const int nq = Q - q0 < DAB_MAX_QUERY_BATCH ? Q - q0 : DAB_MAX_QUERY_BATCH;
-        int levels = 0;
-        if (int rc = run_search_chunk(s, sv, s->scratch, q_dev + (size_t)q0 * s->dim, nq, k, allow,
-                                      out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, &levels, st, q0 == 0))
+        if (int rc = run_search_chunk(s, path, spare_rounds, sv, sc, q_dev + (size_t)q0 * s->dim, nq, k, allow,
+                                      out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, st, q0 == 0))
             return rc;
-        s->last_num_levels = levels;
     }
     DAB_CUDA_OK(cudaEventRecord(s->scratch_free, st));
-    if (s->path == 0 && small && s->small_simt_credit > 0) s->small_simt_credit--;   // consumed after the plan was chosen
+    if (path == 0 && small && s->small_simt_credit > 0) s->small_simt_credit--;   // consumed after the plan was chosen
     return DAB_OK;
+}
+
+// Verdict of this thread's last search on `s` (after `st` has been synchronised).
+static int read_verdict(dab_store *s) {
+    if (t_last.store != s || t_last.empty) return DAB_OK;   // nothing searched by this thread, or the store was empty
+    const volatile int *v = s->verdict_ring_host + 2 * (t_last.seq % kVerdictSlots);
+    const int incomplete = v[0], inexact = v[1];
+    if (incomplete)
+        return fail(DAB_E_INCOMPLETE, "search incomplete: a scan round overflowed its candidate buffer more often than the spare "
+                                      "rounds allow; raise dab_store_set_spare_rounds and search again");
+    if (inexact) {
+        if (t_last.small_tensor) {
+            std::lock_guard<std::mutex> g(s->mu);
+            s->small_simt_credit = 64;
+        }
+        return fail(DAB_E_INEXACT, "more than " + std::to_string(kCandCap / 4) +
+                                       " rows lie within the bf16 rescoring margin of the k-th best; search again on the CUDA-core path");
+    }
+    return DAB_OK;
+}
+}  // namespace dab
+
+extern "C" DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow, float *out_scores,
+                                int64_t *out_ids, void *stream) {
+    return dab_store_search_ex(s, q_dev, Q, k, allow, out_scores, out_ids, -1, -1, stream);
+}
+
+extern "C" DAB_API int dab_store_search_ex(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow, float *out_scores,
+                                           int64_t *out_ids, int path, int spare_rounds, void *stream) {
+    if (int rc = check_store(s, "dab_store_search")) return rc;
+    if (int rc = validate_search(s, q_dev, Q, k, out_scores, out_ids)) return rc;
+    if (path > 2 || spare_rounds > 64) return fail(DAB_E_INVALID, "dab_store_search_ex: path must be -1..2, spare_rounds -1..64");
+    if (path == 2 && !umma_supported(s->dim, s->dtype)) return fail(DAB_E_INVALID, "dab_store_search_ex: rows too wide for the tcgen05 path");
+    if (Q == 0) return DAB_OK;
+    return search_impl(s, q_dev, Q, k, allow, out_scores, out_ids, path, spare_rounds, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" DAB_API int dab_store_search_status(dab_store *s, void *stream) {
     if (int rc = check_store(s, "dab_store_search_status")) return rc;
-    std::lock_guard<std::mutex> g(s->mu);
     DAB_CUDA_OK(cudaSetDevice(s->device));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (s->last_num_levels == 0) {  // nothing searched yet, or the store was empty
-        DAB_CUDA_OK(cudaStreamSynchronize(st));
-        return DAB_OK;
-    }
-    SearchCtrl &c = *s->status_host;  // pinned: the copy is a plain DMA, no staging
-    DAB_CUDA_OK(cudaMemcpyAsync(&c, s->scratch.ctrl, sizeof(c), cudaMemcpyDeviceToHost, st));
-    DAB_CUDA_OK(cudaStreamSynchronize(st));
-    if (c.sticky_incomplete)
-        return fail(DAB_E_INCOMPLETE, "search incomplete: candidate buffer overflowed " + std::to_string(c.overflow_events) +
-                                          " time(s); raise dab_store_set_spare_rounds and search again");
-    if (c.sticky_inexact && s->last_small_tensor) s->small_simt_credit = 64;
-    if (c.sticky_inexact)
-        return fail(DAB_E_INEXACT, "more than " + std::to_string(kCandCap / 4) +
-                                       " rows lie within the bf16 rescoring margin of the k-th best; search again on the CUDA-core path");
-    return DAB_OK;
+    // the verdict was written to pinned memory by the search's last kernel: waiting for the stream is all it takes
+    DAB_CUDA_OK(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    return read_verdict(s);
 }
 
 extern "C" DAB_API uint64_t dab_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
@@ -543,7 +583,7 @@ extern "C" DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *
     if (Q < 1 || k < 1 || k > DAB_MAX_K) return fail(DAB_E_INVALID, "dab_store_describe_plan: bad Q or k");
     std::lock_guard<std::mutex> g(s->mu);
     const int nq = Q < DAB_MAX_QUERY_BATCH ? Q : DAB_MAX_QUERY_BATCH;
-    const SearchPlan sp = choose_plan(s, s->size > 0 ? s->size : 1, s->dim, s->dtype, nq, k);
+    const SearchPlan sp = choose_plan(s, s->path, s->size > 0 ? s->size : 1, s->dim, s->dtype, nq, k);
     if (path) *path = sp.path == 2 && sp.qa ? 4 : sp.path == 2 && sp.quad ? 3 : sp.path;
     if (tile_rows) *tile_rows = sp.levels.tile_rows;
     if (num_levels) *num_levels = sp.levels.num_levels;
@@ -553,10 +593,12 @@ extern "C" DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *
     return DAB_OK;
 }
 
-// device address of {sticky_incomplete, sticky_inexact} of the store's last search (for dab_exchange_merge_topk)
+// device address of the {incomplete, inexact} verdict of the calling thread's last search on `s` (for
+// dab_exchange_merge_topk, enqueued behind that search); before any search: a slot that reads {0, 0}
 extern "C" DAB_API const int *dab_store_status_dev(dab_store *s) {
     if (!s) return nullptr;
-    return &s->scratch.ctrl->sticky_incomplete;
+    if (t_last.store != s || t_last.empty) return s->verdict_ring_dev + 2 * kVerdictSlots;   // the extra slot no search writes
+    return s->verdict_ring_dev + 2 * (t_last.seq % kVerdictSlots);
 }
 
 // ---------------------------------------------------------------- host-buffer search (the e2e entry point)
@@ -594,12 +636,12 @@ extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, 
         }
     }
     char *hbase = static_cast<char *>(s->io_host), *dbase = static_cast<char *>(s->io_dev);
-    const int saved_spare = s->spare_rounds, saved_path = s->path;
     int rc = DAB_OK;
     for (int q0 = 0; q0 < Q && rc == DAB_OK; q0 += DAB_MAX_QUERY_BATCH) {
         const int nq = Q - q0 < DAB_MAX_QUERY_BATCH ? Q - q0 : DAB_MAX_QUERY_BATCH;
         memcpy(hbase + L.q, q_host + (size_t)q0 * s->dim, (size_t)nq * s->dim * sizeof(float));
-        int spare = 0;
+        int spare = -1;             // -1 = the store's settings (dab_store_set_spare_rounds / dab_store_set_path)
+        int path = -1;
         bool forced = false;
         int nrun = nq;              // queries in the staging block: the chunk, or its poisoned queries on the exact redo
         std::vector<int> redo;
@@ -608,8 +650,8 @@ extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, 
                 rc = fail(DAB_E_CUDA, std::string("dab_store_search_host: H2D: ") + cudaGetErrorString((cudaError_t)rc));
                 break;
             }
-            rc = dab_store_search(s, reinterpret_cast<const float *>(dbase + L.q), nrun, k, allow_bitmap_dev,
-                                  reinterpret_cast<float *>(dbase + L.scores), reinterpret_cast<int64_t *>(dbase + L.ids), st);
+            rc = dab_store_search_ex(s, reinterpret_cast<const float *>(dbase + L.q), nrun, k, allow_bitmap_dev,
+                                     reinterpret_cast<float *>(dbase + L.scores), reinterpret_cast<int64_t *>(dbase + L.ids), path, spare, st);
             if (rc != DAB_OK) break;
             cudaMemcpyAsync(hbase + L.scores, dbase + L.scores, (size_t)nrun * k * sizeof(float), cudaMemcpyDeviceToHost, st);
             cudaMemcpyAsync(hbase + L.ids, dbase + L.ids, (size_t)nrun * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
@@ -619,7 +661,7 @@ extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, 
                 // final.  Keep those, pack the poisoned ones to the front of the staging block and answer them on
                 // the exact CUDA-core path.
                 forced = true;
-                s->path = 1;
+                path = 1;
                 const float *hs = reinterpret_cast<const float *>(hbase + L.scores);
                 const int64_t *hi = reinterpret_cast<const int64_t *>(hbase + L.ids);
                 redo.clear();
@@ -641,14 +683,11 @@ extern "C" DAB_API int dab_store_search_host(dab_store *s, const float *q_host, 
                 continue;
             }
             if (rc == DAB_E_INCOMPLETE && spare < 64) {   // adversarial row order: retry with spare rounds
-                spare = spare == 0 ? 4 : spare * 2;
-                s->spare_rounds = spare;
+                spare = spare <= 0 ? 4 : spare * 2;
                 continue;
             }
             break;
         }
-        s->spare_rounds = saved_spare;
-        s->path = saved_path;
         if (rc == DAB_OK && redo.empty()) {
             memcpy(out_scores_host + (size_t)q0 * k, hbase + L.scores, (size_t)nq * k * sizeof(float));
             memcpy(out_ids_host + (size_t)q0 * k, hbase + L.ids, (size_t)nq * k * sizeof(int64_t));

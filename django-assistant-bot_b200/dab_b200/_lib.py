@@ -37,6 +37,7 @@ SIGNATURES = {
     "dab_store_export": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dab_store_set_id_base": (c_int, [c_void_p, c_int64]),
     "dab_store_search": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dab_store_search_ex": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "dab_store_search_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dab_store_search_status": (c_int, [c_void_p, c_void_p]),
     "dab_store_set_spare_rounds": (c_int, [c_void_p, c_int]),

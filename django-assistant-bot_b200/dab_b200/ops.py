@@ -200,9 +200,10 @@ class ChunkStore:
 
     # -- read side
     def search_async(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None,
-                     out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
+                     out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, *, path: int = -1, spare_rounds: int = -1):
         """Enqueue the search on the current stream; returns device tensors (scores [Q,k] fp32
-        descending, ids [Q,k] int64).  No host synchronisation.  See ``search`` for the checked form."""
+        descending, ids [Q,k] int64).  No host synchronisation.  See ``search`` for the checked form.
+        ``path`` / ``spare_rounds`` override the store's settings for this call only (-1 = keep)."""
         _need_cuda(queries, "queries")
         if queries.dim() == 1:
             queries = queries[None, :]
@@ -222,8 +223,8 @@ class ChunkStore:
                 raise DabError(_lib.DAB_E_INVALID, "allow bitmap shorter than the store")
             aptr = allow_bitmap.data_ptr()
         with torch.cuda.device(self.device):
-            check(lib().dab_store_search(self._h, queries.data_ptr(), Q, int(k), aptr, scores.data_ptr(), ids.data_ptr(),
-                                         _stream(self.device)))
+            check(lib().dab_store_search_ex(self._h, queries.data_ptr(), Q, int(k), aptr, scores.data_ptr(), ids.data_ptr(),
+                                            int(path), int(spare_rounds), _stream(self.device)))
         return scores, ids
 
     def search_host(self, queries, k: int, allow_bitmap: Optional[torch.Tensor] = None):
@@ -246,53 +247,44 @@ class ChunkStore:
             if allow_bitmap.numel() * 32 < len(self):
                 raise DabError(_lib.DAB_E_INVALID, "allow bitmap shorter than the store")
             aptr = allow_bitmap.data_ptr()
-        # one checked search at a time per store: the verdict word read after a search belongs to the
-        # most recent search on this store (the GIL is released inside the C call)
-        with self._lock, torch.cuda.device(self.device):
+        # (the GIL is released inside the C call; concurrent calls on one store are serialised by the library)
+        with torch.cuda.device(self.device):
             check(lib().dab_store_search_host(self._h, q.ctypes.data, Q, int(k), aptr, scores.ctypes.data, ids.ctypes.data,
                                               _stream(self.device)))
         return scores, ids
 
     def search(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None):
         """Checked search: runs ``search_async``, waits, and if a scan round overflowed its
-        candidate buffer (adversarial row order) repeats with spare rounds until complete."""
-        with self._lock:
-            spare = 0
-            forced_simt = False
-            kept = None
-            try:
-                while True:
-                    scores, ids = self.search_async(queries, k, allow_bitmap)
-                    with torch.cuda.device(self.device):
-                        rc = lib().dab_store_search_status(self._h, _stream(self.device))
-                    if rc == _lib.DAB_E_INEXACT and not forced_simt:
-                        # more rows inside the rescoring margin than the tensor pass can keep, for SOME queries:
-                        # those came back poisoned (NaN score in front), the others are final.  Answer the
-                        # poisoned ones on the exact CUDA-core path and splice them in.
-                        lib().dab_store_set_path(self._h, 1)
-                        forced_simt = True
-                        bad = torch.isnan(scores[:, 0])
-                        n_bad = int(bad.sum())
-                        if 0 < n_bad < scores.shape[0]:
-                            kept = (scores, ids, bad)
-                            queries = (queries if queries.dim() == 2 else queries[None, :])[bad].contiguous()
-                        continue
-                    if rc != _lib.DAB_E_INCOMPLETE:
-                        check(rc)
-                        if kept is not None:
-                            kept[0][kept[2]] = scores
-                            kept[1][kept[2]] = ids
-                            return kept[0], kept[1]
-                        return scores, ids
-                    spare = 4 if spare == 0 else spare * 2
-                    if spare > 64:
-                        raise DabError(_lib.DAB_E_INCOMPLETE, "search did not complete within 64 spare rounds")
-                    self.set_spare_rounds(spare)
-            finally:
-                if spare:
-                    self.set_spare_rounds(0)
-                if forced_simt:
-                    lib().dab_store_set_path(self._h, self._path)
+        candidate buffer (adversarial row order) repeats with spare rounds until complete.
+        Safe to call from several threads on one store: the verdict read belongs to this thread's
+        own call, and the retries pass their path / spare rounds per call instead of changing the store."""
+        spare, path = -1, -1
+        kept = None
+        while True:
+            scores, ids = self.search_async(queries, k, allow_bitmap, path=path, spare_rounds=spare)
+            with torch.cuda.device(self.device):
+                rc = lib().dab_store_search_status(self._h, _stream(self.device))
+            if rc == _lib.DAB_E_INEXACT and path != 1:
+                # more rows inside the rescoring margin than the tensor pass can keep, for SOME queries:
+                # those came back poisoned (NaN score in front), the others are final.  Answer the
+                # poisoned ones on the exact CUDA-core path and splice them in.
+                path = 1
+                bad = torch.isnan(scores[:, 0])
+                n_bad = int(bad.sum())
+                if 0 < n_bad < scores.shape[0]:
+                    kept = (scores, ids, bad)
+                    queries = (queries if queries.dim() == 2 else queries[None, :])[bad].contiguous()
+                continue
+            if rc != _lib.DAB_E_INCOMPLETE:
+                check(rc)
+                if kept is not None:
+                    kept[0][kept[2]] = scores
+                    kept[1][kept[2]] = ids
+                    return kept[0], kept[1]
+                return scores, ids
+            spare = 4 if spare <= 0 else spare * 2
+            if spare > 64:
+                raise DabError(_lib.DAB_E_INCOMPLETE, "search did not complete within 64 spare rounds")
 
 
 def doc_aggregate(scores: torch.Tensor, rows: torch.Tensor, doc_of_row: torch.Tensor, max_scores_n: int, top_n: int):

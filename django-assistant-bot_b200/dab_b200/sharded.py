@@ -96,18 +96,50 @@ class PeerExchange:
         i = self.buf[off_i: off_i + Q * k * 8].view(torch.int64).view(Q, k)
         return s, i
 
-    def merge(self, Q: int, k: int, local_status_ptr: Optional[int]):
+    def _packed(self, Q: int, k: int):
+        """One device block [scores | ids | verdict] and its pinned twin, so that a checked search costs ONE
+        device-to-host copy and ONE stream synchronisation."""
+        key = (Q, k)
+        if getattr(self, "_packed_key", None) != key:
+            off_i = (Q * k * 4 + 15) // 16 * 16
+            off_st = off_i + Q * k * 8
+            total = off_st + 16
+            self._packed_dev = torch.empty(total, dtype=torch.uint8, device=self.device)
+            self._packed_host = torch.empty(total, dtype=torch.uint8).pin_memory()
+            self._packed_off = (off_i, off_st, total)
+            self._packed_key = key
+        return self._packed_dev, self._packed_host, self._packed_off
+
+    def merge(self, Q: int, k: int, local_status_ptr: Optional[int], packed: bool = False):
         """Launch the exchange kernel for the slot handed out last; returns merged (scores, ids) and
-        leaves the OR-ed verdict in ``status_dev``."""
+        leaves the OR-ed verdict in ``status_dev`` (``packed``: everything lands in one device block whose
+        pinned copy ``fetch_packed`` reads back with a single transfer)."""
         from ._lib import check, lib
-        out_s = torch.empty((Q, k), dtype=torch.float32, device=self.device)
-        out_i = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+        if packed:
+            dev_blk, _, (off_i, off_st, _) = self._packed(Q, k)
+            out_s = dev_blk[:Q * k * 4].view(torch.float32).view(Q, k)
+            out_i = dev_blk[off_i:off_i + Q * k * 8].view(torch.int64).view(Q, k)
+            st_ptr = dev_blk.data_ptr() + off_st
+        else:
+            out_s = torch.empty((Q, k), dtype=torch.float32, device=self.device)
+            out_i = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+            st_ptr = self.status_dev.data_ptr()
         with torch.cuda.device(self.device):
             check(lib().dab_exchange_merge_topk(self.bases_dev, self.rank, self.world, self.max_q, self.max_k, Q, k,
                                                 self.epoch, local_status_ptr, out_s.data_ptr(), out_i.data_ptr(),
-                                                self.status_dev.data_ptr(),
-                                                torch.cuda.current_stream(self.device).cuda_stream))
+                                                st_ptr, torch.cuda.current_stream(self.device).cuda_stream))
         return out_s, out_i
+
+    def fetch_packed(self, Q: int, k: int):
+        """After ``merge(packed=True)``: one D2H copy + one synchronise.  Returns host views
+        (scores [Q,k], ids [Q,k], incomplete, inexact)."""
+        dev_blk, host_blk, (off_i, off_st, _) = self._packed(Q, k)
+        host_blk.copy_(dev_blk, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        s = host_blk[:Q * k * 4].view(torch.float32).view(Q, k)
+        i = host_blk[off_i:off_i + Q * k * 8].view(torch.int64).view(Q, k)
+        st = host_blk[off_st:off_st + 8].view(torch.int32)
+        return s, i, bool(st[0]), bool(st[1])
 
     def verdict(self) -> Tuple[bool, bool]:
         """(incomplete, inexact) of the last exchange, identical on every rank.  Synchronises."""
@@ -144,50 +176,41 @@ class ShardedStore:
         self.local.append(rows)
 
     def _search_p2p(self, queries: torch.Tensor, k: int, allow_bitmap):
-        from ._lib import lib
+        from ._lib import DabError, lib
         if queries.dim() == 1:
             queries = queries[None, :]
         Q = queries.shape[0]
-        spare, forced_simt = 0, False
+        spare, path = -1, -1
         kept = None
-        try:
-            while True:
-                slot = self.peer.next_slot(Q, k)
-                self.local.search_async(queries, k, allow_bitmap, out=slot)
-                s, i = self.peer.merge(Q, k, lib().dab_store_status_dev(self.local._h))
-                incomplete, inexact = self.peer.verdict()          # same answer on every rank
-                if inexact and not forced_simt:
-                    # Some rank's tensor pass could not keep every row inside the rescoring margin for SOME
-                    # queries; that rank's lists for them are poisoned (NaN in front).  The union over the ranks
-                    # (every rank is here: the verdict is OR-ed) is repeated on the exact CUDA-core path by all
-                    # ranks together; the other queries' merged answers are final.
-                    lib().dab_store_set_path(self.local._h, 1)
-                    forced_simt = True
-                    bad = torch.isnan(slot[0][:, 0]).to(torch.int32)
-                    dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=self.group)
-                    bad = bad.bool()
-                    n_bad = int(bad.sum())
-                    if 0 < n_bad < Q:
-                        kept = (s, i, bad)
-                        queries = queries[bad].contiguous()
-                        Q = n_bad
-                    continue
-                if not incomplete:
-                    if kept is not None:
-                        kept[0][kept[2]] = s
-                        kept[1][kept[2]] = i
-                        return kept[0], kept[1]
-                    return s, i
-                spare = 4 if spare == 0 else spare * 2
-                if spare > 64:
-                    from ._lib import DabError
-                    raise DabError(5, "sharded search did not complete within 64 spare rounds")
-                self.local.set_spare_rounds(spare)
-        finally:
-            if spare:
-                self.local.set_spare_rounds(0)
-            if forced_simt:
-                lib().dab_store_set_path(self.local._h, self.local._path)
+        while True:
+            slot = self.peer.next_slot(Q, k)
+            self.local.search_async(queries, k, allow_bitmap, out=slot, path=path, spare_rounds=spare)
+            s, i = self.peer.merge(Q, k, lib().dab_store_status_dev(self.local._h))
+            incomplete, inexact = self.peer.verdict()          # same answer on every rank
+            if inexact and path != 1:
+                # Some rank's tensor pass could not keep every row inside the rescoring margin for SOME
+                # queries; that rank's lists for them are poisoned (NaN in front).  The union over the ranks
+                # (every rank is here: the verdict is OR-ed) is repeated on the exact CUDA-core path by all
+                # ranks together; the other queries' merged answers are final.
+                path = 1
+                bad = torch.isnan(slot[0][:, 0]).to(torch.int32)
+                dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=self.group)
+                bad = bad.bool()
+                n_bad = int(bad.sum())
+                if 0 < n_bad < Q:
+                    kept = (s, i, bad)
+                    queries = queries[bad].contiguous()
+                    Q = n_bad
+                continue
+            if not incomplete:
+                if kept is not None:
+                    kept[0][kept[2]] = s
+                    kept[1][kept[2]] = i
+                    return kept[0], kept[1]
+                return s, i
+            spare = 4 if spare <= 0 else spare * 2
+            if spare > 64:
+                raise DabError(5, "sharded search did not complete within 64 spare rounds")
 
     def search(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None):
         """Replicated queries in, identical merged ``(scores [Q,k], ids [Q,k])`` out on every rank."""
@@ -200,6 +223,37 @@ class ShardedStore:
         s, i = self.local.search(queries, k, allow_bitmap)
         gs, gi = gather_topk(s, i, self.group)
         return ops.merge_topk(gs, gi)
+
+    def search_host(self, queries_host, k: int, allow_bitmap: Optional[torch.Tensor] = None, out=None):
+        """The reference-facing form on every rank: HOST queries in (a float32 tensor, ideally pinned; or anything
+        ``torch.as_tensor`` accepts, e.g. the Python list ``_objects_embedding_search`` receives,
+        assistant/rag/services/search_service.py:186), HOST ``(scores [Q,k], ids [Q,k])`` out.  On the peer-memory
+        transport the merged lists and the OR-ed verdict come back in one device-to-host copy and one
+        synchronise; the rare verdicts (inexact / incomplete) fall back to the checked device search."""
+        q = torch.as_tensor(queries_host, dtype=torch.float32)
+        if q.dim() == 1:
+            q = q[None, :]
+        Q = q.shape[0]
+        qd = q.to(self.local.device, non_blocking=True)
+        if self.world > 1 and self.peer is not None and self.peer.fits(Q, k):
+            from ._lib import lib
+            slot = self.peer.next_slot(Q, k)
+            self.local.search_async(qd, k, allow_bitmap, out=slot)
+            self.peer.merge(Q, k, lib().dab_store_status_dev(self.local._h), packed=True)
+            s, i, incomplete, inexact = self.peer.fetch_packed(Q, k)
+            if not (incomplete or inexact):
+                if out is not None:
+                    out[0].copy_(s)
+                    out[1].copy_(i)
+                    return out
+                return s.clone(), i.clone()
+        s, i = self.search(qd, k, allow_bitmap)
+        if out is None:
+            out = (torch.empty(s.shape, dtype=s.dtype).pin_memory(), torch.empty(i.shape, dtype=i.dtype).pin_memory())
+        out[0].copy_(s, non_blocking=True)
+        out[1].copy_(i, non_blocking=True)
+        torch.cuda.current_stream(self.local.device).synchronize()
+        return out
 
     def close(self) -> None:
         self.local.close()

@@ -15,7 +15,7 @@
  *   - the library owns only what dab_store_create allocates (rows, inverse norms, ids,
  *     per-store scratch) and frees it in dab_store_destroy.
  *   - thread safety: calls on different stores are independent; calls on one store are
- *     serialised by a per-store mutex (the reference reaches this code from an asgiref
+ *     serialised by a per-store mutex and every search keeps its own verdict (the reference reaches this code from an asgiref
  *     worker thread, assistant/rag/services/search_service.py:191, and from uvicorn
  *     workers, gpu_service/gunicorn_conf.py:9).
  */
@@ -90,6 +90,7 @@ DAB_API int dab_pool_l2norm(const void *hidden_dev, int hidden_dtype, const void
  * and :13 (Document.content_embedding).  Only non-NULL embeddings are stored.
  *   dtype: DAB_F32 (what pgvector stores) or DAB_BF16.  Synchronous (allocates).
  */
+/* capacity_rows: 1 .. 2^31-1 */
 DAB_API int dab_store_create(dab_store **out, int device, int64_t capacity_rows, int dim, int dtype);
 DAB_API void dab_store_destroy(dab_store *s);
 
@@ -158,6 +159,14 @@ DAB_API int dab_store_set_id_base(dab_store *s, int64_t id_base);
 DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
                      float *out_scores_dev, int64_t *out_ids_dev, void *stream);
 /*
+ * dab_store_search with the scoring path and the number of spare rounds given for THIS call (-1 = the store's
+ * setting), instead of through dab_store_set_path / dab_store_set_spare_rounds, which change the store for
+ * every thread.  What a checked wrapper uses to repeat a search after DAB_E_INEXACT (path 1) or
+ * DAB_E_INCOMPLETE (spare rounds) while other threads keep searching the same store.
+ */
+DAB_API int dab_store_search_ex(dab_store *s, const float *q_dev, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
+                                float *out_scores_dev, int64_t *out_ids_dev, int path, int spare_rounds, void *stream);
+/*
  * The same search with HOST buffers, complete and checked: what the reference-facing call uses
  * (`_objects_embedding_search` receives the query as a Python list, search_service.py:186).
  * Copies the queries to the device (pinned staging owned by the store, allocated on first use),
@@ -166,8 +175,10 @@ DAB_API int dab_store_search(dab_store *s, const float *q_dev, int Q, int k, con
  */
 DAB_API int dab_store_search_host(dab_store *s, const float *q_host, int Q, int k, const uint32_t *allow_bitmap_dev_or_null,
                                   float *out_scores_host, int64_t *out_ids_host, void *stream);
-/* Synchronises `stream`; DAB_OK, DAB_E_INCOMPLETE or DAB_E_INEXACT for the last search call on `s`
- * (all of its query chunks). */
+/* Synchronises `stream`; DAB_OK, DAB_E_INCOMPLETE or DAB_E_INEXACT for the last search call THE CALLING THREAD
+ * made on `s` (all of its query chunks).  Verdicts are kept per call (a ring of 256 per store, written by the
+ * search's last kernel into pinned memory), so searches other threads enqueue on the same store in between do
+ * not disturb it. */
 DAB_API int dab_store_search_status(dab_store *s, void *stream);
 /* extra scan rounds enqueued per search for overflow retries (default 0) */
 DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds);
@@ -218,7 +229,7 @@ DAB_API int dab_doc_aggregate(const float *scores_dev, const int64_t *rows_dev, 
  */
 DAB_API int64_t dab_exchange_bytes(int R, int max_q, int max_k);
 DAB_API int dab_exchange_slot(void *base, int R, int max_q, int max_k, uint32_t epoch, float **scores, int64_t **ids);
-DAB_API const int *dab_store_status_dev(dab_store *s);
+DAB_API const int *dab_store_status_dev(dab_store *s);   /* verdict slot of the calling thread's last search on s */
 DAB_API int dab_exchange_merge_topk(void *const *peer_bases_dev, int rank, int R, int max_q, int max_k, int Q, int k,
                                     uint32_t epoch, const int *local_status_dev_or_null, float *out_scores_dev,
                                     int64_t *out_ids_dev, int *out_status_dev_or_null, void *stream);
@@ -241,7 +252,10 @@ DAB_API int dab_exchange_merge_topk(void *const *peer_bases_dev, int rank, int R
  * loading the library holds until exit.  Hence the limits: Q <= DAB_NOALLOC_MAX_QUERIES,
  * dim <= DAB_NOALLOC_MAX_DIM, else DAB_E_CAPACITY.  All calls on a device share that array:
  * each call resets the state it reads, but calls that overlap on the GPU (two streams) race -
- * keep them on one stream or order them with events.  The first call on a device resolves the
+ * keep them on one stream or order them with events.  One call is a sequence of kernel launches;
+ * the library holds a per-device host mutex while it enqueues them, so host threads that share a
+ * stream cannot interleave two calls' launches - threads on different streams must still order
+ * those streams themselves (the mutex does not wait for the GPU).  The first call on a device resolves the
  * array's address (cudaGetSymbolAddress): issue it before any stream capture.  Asynchronous;
  * makes no cudaMalloc/cudaFree.  DAB_NOALLOC_SPARE_ROUNDS retry rounds are always enqueued; a
  * search that still overflowed writes id -1 / NaN (check the first id).

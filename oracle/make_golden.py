@@ -130,11 +130,51 @@ def make_search_golden():
     print("search_ref.npz: sims", sims.shape)
 
 
+def make_search_golden_bf16():
+    """A second, larger retrieval fixture: the rows are bf16-representable values (what a bf16 store holds, upcast
+    exactly), the reference's own ``embeddings_similarity`` (search_service.py:32-35, float64 NumPy on Python lists)
+    ranks them, and n = 50 > 10.  Rows regenerate from the seed, so only queries and reference outputs are stored."""
+    from assistant.rag.services import search_service as ss  # the reference module
+    from oracle import search_ref
+
+    rng = np.random.default_rng(8765)
+    N, D, Q, n = 400, 768, 6, 50
+    rows = search_ref.bf16_bits_to_f32(search_ref.f32_to_bf16_bits(rng.standard_normal((N, D)).astype(np.float32)))
+    rows[150] = rows[9]            # duplicates inside the top of query 0's list
+    rows[151] = rows[9]
+    rows[200] = 0                  # zero vector: NaN similarity, never ranked
+    queries = rng.standard_normal((Q, D)).astype(np.float32)
+    queries[0] = rows[9] + 0.01 * queries[0]
+    queries[1] = 7.0 * rows[33]    # un-normalised query, identical direction
+    sims = np.empty((Q, N), dtype=np.float64)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        for qi in range(Q):
+            for r in range(N):
+                sims[qi, r] = ss.embeddings_similarity(queries[qi].tolist(), rows[r].tolist())
+    np.savez_compressed(os.path.join(OUT, "search_ref_bf16.npz"), seed=8765, shape=np.array([N, D, Q, n]), queries=queries,
+                        sims=sims, row_checksum=np.array([float(rows.astype(np.float64).sum())]))
+    print("search_ref_bf16.npz: sims", sims.shape)
+
+
+def golden_bf16_rows():
+    """The rows of search_ref_bf16.npz, regenerated (tests call this; it needs nothing from the reference)."""
+    from oracle import search_ref
+    rng = np.random.default_rng(8765)
+    N, D = 400, 768
+    rows = search_ref.bf16_bits_to_f32(search_ref.f32_to_bf16_bits(rng.standard_normal((N, D)).astype(np.float32)))
+    rows[150] = rows[9]
+    rows[151] = rows[9]
+    rows[200] = 0
+    return rows
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("needs /root/reference (run in the build container)")
     os.makedirs(OUT, exist_ok=True)
     sys.path.insert(0, REF)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # `from oracle import ...`
     _stub_modules()
     make_pool_golden()
     make_search_golden()
+    make_search_golden_bf16()

@@ -45,6 +45,26 @@ def test_search_matches_reference_golden(golden_dir):
     store.close()
 
 
+@pytest.mark.parametrize("path", ["simt", "tcgen05"])
+def test_bf16_store_matches_reference_golden_top50(golden_dir, path):
+    """A bf16 store against numbers the REFERENCE computed (embeddings_similarity on the same bf16-valued rows,
+    tests/golden/search_ref_bf16.npz): n = 50, a triplicated row, a zero row, an un-normalised query."""
+    from dab_b200 import ops
+    from oracle import make_golden
+    g = np.load(os.path.join(golden_dir, "search_ref_bf16.npz"))
+    rows, queries, sims = make_golden.golden_bf16_rows(), g["queries"], g["sims"]
+    store = ops.ChunkStore(rows.shape[0], rows.shape[1], torch.bfloat16, DEV)
+    store.set_path(path)
+    store.append(torch.from_numpy(rows).to(DEV))          # bf16-representable values: the rounding is exact
+    scores, ids = store.search(torch.from_numpy(queries).to(DEV), 50)
+    for qi in range(queries.shape[0]):
+        search_ref.check_topk_parity(sims[qi], ids[qi].cpu().numpy(), scores[qi].cpu().numpy(), 50)
+    assert ids[0, :3].tolist() == [9, 150, 151]
+    assert ids[1, 0].item() == 33 and abs(scores[1, 0].item() - 1.0) < 1e-6
+    assert 200 not in ids.cpu().numpy()
+    store.close()
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("N,D,Q,k", [(10_000, 384, 1, 10), (50_000, 768, 1, 10), (50_000, 768, 4, 100),
                                      (30_011, 1024, 3, 5), (200_000, 768, 2, 250), (777, 64, 7, 1), (5, 128, 2, 10),

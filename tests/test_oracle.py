@@ -200,3 +200,19 @@ def test_ranking_invariants(seed):
     scale = rng.uniform(0.1, 10, size=(N, 1)).astype(np.float32)
     S3 = search_ref.exact_scores(rows * scale, 3.0 * q)[0]
     search_ref.check_topk_parity(S, search_ref.rank_topk(S3, k)[0], S3[search_ref.rank_topk(S3, k)[0]], k)
+
+
+def test_bf16_golden_rows_regenerate_and_oracle_matches_reference(golden_dir):
+    """search_ref_bf16.npz stores only the reference's outputs; the bf16-valued rows come back from the seed
+    (checksum pinned) and the oracle's float64 cosine must reproduce the reference's numbers on them."""
+    from oracle import make_golden
+    g = np.load(os.path.join(golden_dir, "search_ref_bf16.npz"))
+    rows = make_golden.golden_bf16_rows()
+    assert float(rows.astype(np.float64).sum()) == float(g["row_checksum"][0])
+    S = search_ref.exact_scores(rows, g["queries"])
+    sims = g["sims"]
+    assert np.isnan(sims[:, 200]).all() and np.isnan(S[:, 200]).all()          # the zero row
+    ok = ~np.isnan(sims)
+    np.testing.assert_allclose(S[ok], sims[ok], rtol=1e-12, atol=1e-12)
+    ids, _ = search_ref.rank_topk(sims[0], 50)
+    assert ids[:3].tolist() == [9, 150, 151]                                    # triplicate: index order

@@ -5,7 +5,7 @@ spoken for (the embedding service, after the encoder's allocator has reserved th
 from a request handler where cudaMalloc's device-wide synchronisation is unaffordable.  They hand
 in their own row matrix, inverse norms and output buffers; the search scratch is a static device
 array inside the library.  This file checks, through the C-ABI, that such a call returns what the
-ordinary store-based search returns on the same rows - twice in a row, because every call reuses
+ordinary store-based search returns on the same rows, and what the CPU oracle says - twice in a row, because every call reuses
 the same static scratch and must not be confused by what the previous call left there.
 
 Named test_zz_* so pytest collects it last: a run that stops at the first failure has then
@@ -48,6 +48,16 @@ def _same_ranking(ids_a, sc_a, ids_b, sc_b):
                 assert abs(sc_a[q, j] - sc_b[q, j]) < 1e-6, (q, j, ids_a[q, j], ids_b[q, j])
 
 
+def _matches_oracle(rows, queries, ids, scores, k, id_base, allow=None):
+    """Pins the answer to the CPU oracle itself (float64 cosine of the STORED values, bf16 upcast exactly), so a
+    fault shared by both entry points - they run the same kernels - cannot pass unnoticed."""
+    from oracle import search_ref
+    S = search_ref.exact_scores(rows.float().cpu().numpy(), queries.cpu().numpy())
+    got_i, got_s = ids.cpu().numpy() - id_base, scores.cpu().numpy()
+    for qi in range(queries.shape[0]):
+        search_ref.check_topk_parity(S[qi], got_i[qi], got_s[qi], k, None if allow is None else allow.numpy())
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_noalloc_matches_store_search_twice_in_a_row(dtype):
     from dab_b200 import _lib, ops
@@ -68,6 +78,7 @@ def test_noalloc_matches_store_search_twice_in_a_row(dtype):
     assert rc == 0, _lib.lib().dab_last_error()
     ws1, wi1 = store.search(q1, 10)
     _same_ranking(i1, s1, wi1, ws1)
+    _matches_oracle(rows, q1, i1, s1, 10, 1000)
     assert 1123 not in i1.cpu().numpy()
 
     # second call straight after, different batch size, k and a row filter: the static scratch
@@ -79,6 +90,7 @@ def test_noalloc_matches_store_search_twice_in_a_row(dtype):
     assert rc == 0, _lib.lib().dab_last_error()
     ws2, wi2 = store.search(q2, 100, bitmap)
     _same_ranking(i2, s2, wi2, ws2)
+    _matches_oracle(rows, q2, i2, s2, 100, 1000, allow)
     assert allow.numpy()[(i2.cpu().numpy() - 1000).ravel()].all()
 
     # and the first question again: same answer as before
