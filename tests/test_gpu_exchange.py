@@ -1,5 +1,6 @@
 """dab_exchange_merge_topk on one GPU (world size 1: publish, wait and gather all hit the local block)."""
 import ctypes
+import time
 
 import numpy as np
 import pytest
@@ -84,7 +85,7 @@ def test_exchange_two_ranks_on_one_gpu_publish_wait_pull():
                 slot = (blocks[r][off_s: off_s + Q * k * 4].view(torch.float32).view(Q, k),
                         blocks[r][off_i: off_i + Q * k * 8].view(torch.int64).view(Q, k))
                 if r == 1:
-                    torch.cuda._sleep(20_000_000)    # rank 0's kernel is already waiting for this rank's flag
+                    time.sleep(0.05)                 # rank 0's kernel is already on the GPU, waiting for this rank's flag
                 stores[r].search_async(qd, k, out=slot)
                 out_s = torch.empty(Q, k, device=DEV)
                 out_i = torch.empty(Q, k, dtype=torch.int64, device=DEV)
