@@ -36,8 +36,16 @@ namespace {
 
 using namespace umma;
 constexpr int kThreads = 384;         // warps 0-3: roles; warps 4-11: epilogue (two per TMEM lane quarter)
+#ifndef DAB_QUAD_KBS
+#define DAB_QUAD_KBS 2
+#endif
+#ifndef DAB_QUAD_ARM_AHEAD
+#define DAB_QUAD_ARM_AHEAD 1
+#endif
+constexpr int kKbPerStage = DAB_QUAD_KBS;                 // 128-byte k-blocks per shared-memory stage: one barrier round per
+constexpr int kStageBytes = kKbPerStage * kAStageBytes;   // kKbPerStage * 4 MMAs instead of per 4 (the issuer's wait is not free)
 constexpr int kMaxStages = 12;
-constexpr int kMinStages = 3;
+constexpr int kMinStages = kKbPerStage == 1 ? 3 : 2;
 constexpr int kMaxAcc = 4;         // TMEM accumulator stages (512 columns / n_pair, at most 4)
 constexpr int kEpiWarps = 8;
 constexpr int kWarpCap = 64;        // staged candidates per epilogue warp per tile (more go straight to the candidate buffer)
@@ -70,9 +78,10 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     const int num_kb = (sv.dim + kb_elems - 1) / kb_elems;   // partial last k-block: zero-filled by TMA
     const int b_kb_bytes = n_half * 128;
     unsigned char *b_smem = smem;                                              // [num_kb][n_half rows x 128 B]
-    unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;              // [stages][128 rows x 128 B]
-    float *tau_s = reinterpret_cast<float *>(a_smem + (size_t)stages * kAStageBytes);  // [256]
-    uint64_t *full = reinterpret_cast<uint64_t *>(tau_s + DAB_MAX_QUERY_BATCH);        // leaders: both A halves landed
+    unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;              // [stages][kKbPerStage][128 rows x 128 B]
+    float *tau_s = reinterpret_cast<float *>(a_smem + (size_t)stages * kStageBytes);   // [256]
+    float *ntau_s = tau_s + DAB_MAX_QUERY_BATCH;                                        // [256] negated thresholds
+    uint64_t *full = reinterpret_cast<uint64_t *>(ntau_s + DAB_MAX_QUERY_BATCH);       // leaders: both A halves landed
     uint64_t *empty = full + kMaxStages;               // ranks 0/1: both pairs are done with the stage
     uint64_t *b_full = empty + kMaxStages;             // this CTA's query quarter landed
     uint64_t *b_pair = b_full + 1;                     // leaders: both quarters of the pair landed
@@ -109,12 +118,14 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
     for (int q = tid; q < DAB_MAX_QUERY_BATCH; q += kThreads) {
         const bool live = q < nq && sc.active[q0 + q];
         tau_s[q] = live ? key_score(sc.tau_key[q0 + q]) : INFINITY;
+        ntau_s[q] = -tau_s[q];
     }
     tc_fence_before();
     cluster_sync_all();   // barriers of every CTA are initialised before any remote arrive / multicast
     tc_fence_after();
     const uint32_t tmem_base = warp_uniform(*tmem_base_s);
     const long long my_tiles = (ntiles - cluster_id + num_clusters - 1) / num_clusters;
+    const int spt = (num_kb + kKbPerStage - 1) / kKbPerStage;   // stage uses per super-tile (the last may hold fewer k-blocks)
 
     if (warp == 0) {
         if (elect_one()) {
@@ -131,13 +142,19 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                 for (long long it = 0; it < my_tiles; it++) {
                     const long long t = level_tile(plan, lvl, cluster_id + it * num_clusters);
                     const int row0 = (int)(t * kSuperRows) + half * kTileRows;
-                    for (int kb = 0; kb < num_kb; kb++) {
+                    for (int j = 0; j < spt; j++) {
                         mbar_wait_bounded(&empty[s], ph ^ 1u);
-
-                        if (num_pairs == 2)
-                            tma_load_2d_mc2(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s], mask);
-                        else
-                            tma_load_2d_2cta(a_smem + (size_t)s * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s]);
+                        unsigned char *dst = a_smem + (size_t)s * kStageBytes;
+#pragma unroll
+                        for (int kk = 0; kk < kKbPerStage; kk++) {
+                            const int kb = j * kKbPerStage + kk;
+                            if (kb < num_kb) {
+                                if (num_pairs == 2)
+                                    tma_load_2d_mc2(dst + kk * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s], mask);
+                                else
+                                    tma_load_2d_2cta(dst + kk * kAStageBytes, &tmap_rows, kb * kb_elems, row0, &full[s]);
+                            }
+                        }
                         if (++s == stages) { s = 0; ph ^= 1u; }
                     }
                 }
@@ -152,25 +169,46 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             tc_fence_after();
             int s = 0;
             uint32_t ph = 0;
+            // both halves of a stage (mine and my peer's), every k-block of it, report to the leader's barrier
+            auto stage_bytes = [&](int j) { return (uint32_t)(2 * kAStageBytes * min(kKbPerStage, num_kb - j * kKbPerStage)); };
+#if DAB_QUAD_ARM_AHEAD
+            // The barrier of stage use u+1 is armed BEFORE waiting for use u: its previous phase completed a ring ago,
+            // so the arm never sits between this thread and the data it is waiting for.
+            mbar_arrive_expect_tx(&full[0], stage_bytes(0));
+#endif
             for (long long it = 0; it < my_tiles; it++) {
                 const int a = (int)(it % acc_stages);
                 const uint32_t aph = (uint32_t)((it / acc_stages) & 1);
                 mbar_wait_bounded(&tmem_empty[a], aph ^ 1u);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(a * n_pair);
-                for (int kb = 0; kb < num_kb; kb++) {
-                    // both 16 KiB halves of the stage (mine and my peer's) report to this barrier
-                    mbar_arrive_expect_tx(&full[s], 2 * kAStageBytes);
+                for (int j = 0; j < spt; j++) {
+#if DAB_QUAD_ARM_AHEAD
+                    {
+                        const bool last = j + 1 == spt;
+                        if (!last || it + 1 < my_tiles)
+                            mbar_arrive_expect_tx(&full[s + 1 == stages ? 0 : s + 1], stage_bytes(last ? 0 : j + 1));
+                    }
+#else
+                    mbar_arrive_expect_tx(&full[s], stage_bytes(j));
+#endif
                     mbar_wait_bounded(&full[s], ph);
                     tc_fence_after();
-                    const uint64_t da = make_smem_desc(smem_u32(a_smem + (size_t)s * kAStageBytes));
-                    const uint64_t db = make_smem_desc(smem_u32(b_smem + (size_t)kb * b_kb_bytes));
+                    const uint32_t a_base = smem_u32(a_smem + (size_t)s * kStageBytes);
 #pragma unroll
-                    for (int k = 0; k < (kBlockK / kUmmaK); k++)
-                        if constexpr (F32)
-                            umma_tf32_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
-                        else
-                            umma_f16_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    for (int kk = 0; kk < kKbPerStage; kk++) {
+                        const int kb = j * kKbPerStage + kk;
+                        if (kb < num_kb) {
+                            const uint64_t da = make_smem_desc(a_base + kk * kAStageBytes);
+                            const uint64_t db = make_smem_desc(smem_u32(b_smem + (size_t)kb * b_kb_bytes));
+#pragma unroll
+                            for (int k = 0; k < kBlockK / kUmmaK; k++)
+                                if constexpr (F32)
+                                    umma_tf32_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                                else
+                                    umma_f16_2cta(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                    }
                     umma_commit_mc2(&empty[s], (uint16_t)0x3u);        // the loaders are ranks 0 and 1
                     if (++s == stages) { s = 0; ph ^= 1u; }
                 }
@@ -221,7 +259,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             const int ew = warp - 4;                                // 0..7
             const WarpList wl = {pend_key + pl * kPendCap + ew * kWarpCap, pend_q + pl * kPendCap + ew * kWarpCap, kWarpCap};
             uint32_t hits = 0;
-            hits = epilogue_tile_wl(taddr, c_count, rinv, row, tau_s + c_begin, q0 + c_begin, allow, sc, wl);
+            hits = epilogue_tile_wl(taddr, c_count, rinv, row, tau_s + c_begin, ntau_s + c_begin, q0 + c_begin, allow, sc, wl);
             row = row_next;
             rinv = rinv_next;
             tc_fence_before();
@@ -252,17 +290,17 @@ bool plan_quad(int dim, int nq, int num_pairs, int elem_bytes, QuadPlan *out) {
     if (n_pair < 32) n_pair = 32;
     if (n_pair > 128) return false;
     const size_t b_bytes = (size_t)(n_pair / 2) * (((size_t)dim * elem_bytes + 127) / 128 * 128);
-    const size_t fixed = DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 + 2 * kEpiWarps * sizeof(uint32_t) +
+    const size_t fixed = 2 * DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 16) * sizeof(uint64_t) + 16 + 2 * kEpiWarps * sizeof(uint32_t) +
                          2 * kPendCap * (sizeof(uint64_t) + sizeof(uint32_t)) + 1024;
-    if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
-    int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
+    if (b_bytes + fixed + (size_t)kMinStages * kStageBytes > (size_t)kSmemBudget) return false;
+    int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kStageBytes);
     if (stages > kMaxStages) stages = kMaxStages;
     // all 512 TMEM columns: as many accumulator stages as fit (2..4) decouple the MMAs from epilogue jitter
     int cols = 512;
     out->n_pair = n_pair;
     out->stages = stages;
     out->tmem_cols = cols;
-    out->smem = b_bytes + (size_t)stages * kAStageBytes + fixed;
+    out->smem = b_bytes + (size_t)stages * kStageBytes + fixed;
     return true;
 }
 

@@ -137,10 +137,45 @@ __device__ __forceinline__ uint32_t pick16(const uint32_t (&v)[16], int j) {
     return x;
 }
 
+// Packed fp32 arithmetic of sm_100 (SASS FFMA2 / FMNMX3): two fused multiply-adds per instruction, a 3-input max.
+__device__ __forceinline__ void ffma2(float &d0, float &d1, float a0, float a1, float b, float c0, float c1) {
+    asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+        "mov.b64 ra, {%2, %3};\n\t"
+        "mov.b64 rb, {%4, %4};\n\t"
+        "mov.b64 rc, {%5, %6};\n\t"
+        "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
+        "mov.b64 {%0, %1}, rd;\n\t}"
+        : "=f"(d0), "=f"(d1)
+        : "f"(a0), "f"(a1), "f"(b), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
 // 16-column slab of an accumulator row (lane = corpus row, column = query).  Returns the new count.
+// Nearly every score fails its threshold (~1 in 1000 passes), so the slab is first screened with
+// m = max_j (v_j * rinv - tau_j): 8 packed FMAs + 8 three-input maxima + one vote per 512 scores, against a
+// multiply, a compare and a mask update for every score.  `ntau_s` holds the NEGATED thresholds.  Only when some
+// lane's m comes within 1e-6 of passing does the warp run the exact per-score test below (the screen is
+// conservative: the exact test decides).
 __device__ __forceinline__ uint32_t epilogue_slab_wl(const uint32_t (&v)[16], int c0, float rinv, long long row,
-                                                     const float *tau_s, int q_base, const uint32_t *__restrict__ allow,
-                                                     const SearchScratch &sc, const WarpList &wl, uint32_t cnt) {
+                                                     const float *tau_s, const float *ntau_s, int q_base,
+                                                     const uint32_t *__restrict__ allow, const SearchScratch &sc,
+                                                     const WarpList &wl, uint32_t cnt) {
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+        const float4 nt = *reinterpret_cast<const float4 *>(ntau_s + c0 + j);
+        float d0, d1, d2, d3;
+        ffma2(d0, d1, __uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]), rinv, nt.x, nt.y);
+        ffma2(d2, d3, __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]), rinv, nt.z, nt.w);
+        m = max3(m, d0, d1);
+        m = max3(m, d2, d3);
+    }
+    // zero rows and rows past the end never rank (rinv = 0, or -0.0 for a tombstone)
+    if (!__any_sync(0xffffffffu, m >= -1e-6f && rinv > 0.f)) return cnt;
     uint32_t pass = 0;
 #pragma unroll
     for (int j = 0; j < 16; j += 4) {
@@ -174,8 +209,8 @@ __device__ __forceinline__ uint32_t epilogue_slab_wl(const uint32_t (&v)[16], in
 
 // whole accumulator row over `ncols` columns (multiple of 16, warp-uniform); returns the warp's hit count
 __device__ __forceinline__ uint32_t epilogue_tile_wl(uint32_t taddr, int ncols, float rinv, long long row, const float *tau_s,
-                                                     int q_base, const uint32_t *__restrict__ allow, const SearchScratch &sc,
-                                                     const WarpList &wl) {
+                                                     const float *ntau_s, int q_base, const uint32_t *__restrict__ allow,
+                                                     const SearchScratch &sc, const WarpList &wl) {
     uint32_t cnt = 0;
     if (ncols <= 0) return cnt;
     uint32_t v0[16], v1[16];
@@ -184,11 +219,11 @@ __device__ __forceinline__ uint32_t epilogue_tile_wl(uint32_t taddr, int ncols, 
         tmem_ld_wait();
         const bool second = c0 + 16 < ncols;
         if (second) tmem_ld16(taddr + (uint32_t)(c0 + 16), v1);
-        cnt = epilogue_slab_wl(v0, c0, rinv, row, tau_s, q_base, allow, sc, wl, cnt);
+        cnt = epilogue_slab_wl(v0, c0, rinv, row, tau_s, ntau_s, q_base, allow, sc, wl, cnt);
         if (second) {
             tmem_ld_wait();
             if (c0 + 32 < ncols) tmem_ld16(taddr + (uint32_t)(c0 + 32), v0);
-            cnt = epilogue_slab_wl(v1, c0 + 16, rinv, row, tau_s, q_base, allow, sc, wl, cnt);
+            cnt = epilogue_slab_wl(v1, c0 + 16, rinv, row, tau_s, ntau_s, q_base, allow, sc, wl, cnt);
         }
     }
     return cnt;
