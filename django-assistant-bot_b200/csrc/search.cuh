@@ -78,10 +78,4 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
                           const LevelPlan &plan, int num_sms, cudaStream_t st, int num_pairs = 2);
 
 
-// wide query blocks, queries as the A operand in TMEM (2-CTA pairs; dim % 128 == 0, dim <= 768)
-int qa_tile_rows();
-bool qa_supported(int dim, int dtype, int nq);
-int launch_scan_umma_qa(const StoreView &sv, const uint32_t *allow, const SearchScratch &sc, int q0, int nq,
-                        const LevelPlan &plan, int num_sms, cudaStream_t st);
-
 }  // namespace dab

@@ -327,7 +327,6 @@ struct SearchPlan {
     bool quad;       // tcgen05: cluster kernel (cta_group::2 pairs) for query blocks wider than one SM holds
     int pairs;       // cluster kernel: 2 = 4-CTA cluster, tiles multicast to both pairs; 1 = one pair per cluster
     int quad_chunk;  // cluster kernel: queries per launch (the whole block unless it exceeds one cluster's shared memory)
-    bool qa;         // tcgen05: queries-as-A pair kernel for wide query blocks (preferred when it applies)
     int k_cap;       // candidates kept per query between levels
     float margin;    // tensor path: approximate-score margin that is kept for rescoring
     LevelPlan levels;
@@ -356,16 +355,13 @@ SearchPlan choose_plan(const dab_store *s, int path, int64_t n, int dim, int dty
         sp.k_cap = kCandCap / 4;  // 2048 kept candidates per query at most
         // wide blocks that do not fit one SM's shared memory go to the 4-CTA cluster kernel
         static const bool no_quad = tuning_env("DAB_NO_QUAD") != nullptr;  // tuning builds only: query-slice groups instead
-        // queries-as-A kernel: parity-green but measured slower than the cluster kernel; tuning builds only
-        static const bool use_qa = tuning_env("DAB_USE_QA") != nullptr;
         const bool wide = nq > umma_queries_per_pass(dim, dtype);
-        sp.qa = wide && use_qa && qa_supported(dim, dtype, nq);
-        sp.quad = wide && !sp.qa && !no_quad && quad_supported(dim, dtype, nq);
+        sp.quad = wide && !no_quad && quad_supported(dim, dtype, nq);
         sp.quad_chunk = nq;
         // fp32 rows are twice as wide: one cluster holds 192 queries at dim 768, so a 256-query block takes two
         // corpus passes of 128 (still far better than slicing it six ways through the single-CTA kernel)
         const int quad_cap = quad_queries_per_pass(dim, dtype);
-        if (wide && !sp.qa && !no_quad && !sp.quad && quad_cap > 0 && nq > quad_cap) {
+        if (wide && !no_quad && !sp.quad && quad_cap > 0 && nq > quad_cap) {
             const int passes = (nq + quad_cap - 1) / quad_cap;
             sp.quad = true;
             sp.quad_chunk = ((nq + passes - 1) / passes + 63) / 64 * 64;
@@ -376,7 +372,7 @@ SearchPlan choose_plan(const dab_store *s, int path, int64_t n, int dim, int dty
         // for Q = 256 cost 6.0 ms against 4.7 ms.  It also beats the single-CTA kernel once that one's epilogue gets
         // long (Q = 80: 2.89 vs 3.00 ms, Q = 96: 2.91 vs 3.25 ms; equal at Q <= 64).  DAB_PAIR_MIN_Q moves the switch.
         static const int pair_min_q = tuning_env("DAB_PAIR_MIN_Q") ? atoi(tuning_env("DAB_PAIR_MIN_Q")) : 65;
-        if (!sp.qa && !no_quad && nq <= pair_queries_per_pass(dim, dtype) && quad_supported(dim, dtype, nq) &&
+        if (!no_quad && nq <= pair_queries_per_pass(dim, dtype) && quad_supported(dim, dtype, nq) &&
             (wide || (dtype == DAB_BF16 && nq >= pair_min_q))) {
             sp.quad = true;
             sp.pairs = 1;
@@ -384,7 +380,7 @@ SearchPlan choose_plan(const dab_store *s, int path, int64_t n, int dim, int dty
             sp.pairs = 2;
         }
         // levels are sized for ~4k admitted rows per k (random unit vectors put ~3k inside the margin)
-        sp.levels = make_level_plan(n, sp.qa ? qa_tile_rows() : sp.quad ? quad_tile_rows() : umma_tile_rows(),
+        sp.levels = make_level_plan(n, sp.quad ? quad_tile_rows() : umma_tile_rows(),
                                     4 * k < sp.k_cap ? 4 * k : sp.k_cap);
     } else {
         sp.margin = 0.f;
@@ -407,9 +403,7 @@ int run_search_chunk(dab_store *s, int path, int spare_rounds, const StoreView &
                 // one launch scores all nq queries
                 ScanTimer tm(s->prof, st);
                 static const bool pair_mode = tuning_env("DAB_WIDE_PAIRS") != nullptr;  // tuning builds only
-                if (sp.qa) {
-                    if (int rc = launch_scan_umma_qa(sv, allow, sc, 0, nq, plan, s->num_sms, st)) return rc;
-                } else if (sp.quad && sp.pairs == 1) {
+                if (sp.quad && sp.pairs == 1) {
                     if (int rc = launch_scan_umma_quad(sv, allow, sc, 0, nq, plan, s->num_sms, st, 1)) return rc;
                 } else if (sp.quad && sp.quad_chunk < nq) {
                     for (int q0 = 0; q0 < nq; q0 += sp.quad_chunk)
@@ -584,7 +578,7 @@ extern "C" DAB_API int dab_store_describe_plan(dab_store *s, int Q, int k, int *
     std::lock_guard<std::mutex> g(s->mu);
     const int nq = Q < DAB_MAX_QUERY_BATCH ? Q : DAB_MAX_QUERY_BATCH;
     const SearchPlan sp = choose_plan(s, s->path, s->size > 0 ? s->size : 1, s->dim, s->dtype, nq, k);
-    if (path) *path = sp.path == 2 && sp.qa ? 4 : sp.path == 2 && sp.quad ? 3 : sp.path;
+    if (path) *path = sp.path == 2 && sp.quad ? 3 : sp.path;
     if (tile_rows) *tile_rows = sp.levels.tile_rows;
     if (num_levels) *num_levels = sp.levels.num_levels;
     if (growth) *growth = sp.levels.growth;

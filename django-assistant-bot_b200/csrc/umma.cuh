@@ -390,6 +390,15 @@ inline int cached_map(CUtensorMap *out, const void *base, uint64_t rows, uint64_
             }
         }
     }
+    {
+        // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+        // GPU's memory hung the GPU: a tensor map is only ever built over memory of the current device.
+        cudaPointerAttributes pa;
+        int dev = -1;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&pa, base) != cudaSuccess ||
+            pa.type != cudaMemoryTypeDevice || pa.device != dev)
+            return fail(DAB_E_INVALID, "tensor map requested over memory that is not device memory of the current GPU");
+    }
     if (int rc = make_map(out, base, rows, dim, box_rows, f32)) return rc;
     std::lock_guard<std::mutex> g(mu);
     Entry &e = cache[next];

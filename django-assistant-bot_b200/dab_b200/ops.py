@@ -140,7 +140,7 @@ class ChunkStore:
         strides = (c * 8)()
         ref = _lib.ctypes.byref
         check(lib().dab_store_describe_plan(self._h, int(Q), int(k), ref(path), ref(tile), ref(levels), ref(growth), strides))
-        return {"path": {1: "simt", 2: "tcgen05", 3: "tcgen05-cluster", 4: "tcgen05-qa"}[path.value], "tile_rows": tile.value,
+        return {"path": {1: "simt", 2: "tcgen05", 3: "tcgen05-cluster"}[path.value], "tile_rows": tile.value,
                 "num_levels": levels.value, "growth": growth.value, "strides": list(strides)[:levels.value]}
 
     def set_profile(self, on: bool) -> None:

@@ -195,33 +195,3 @@ def test_tf32_cluster_kernel_on_fp32_stores(N, D, Q, k):
         search_ref.check_topk_parity(S[qi], ids[qi], scores[qi], k)
     assert ids[Q - 1, 0] == 17
     store.close()
-
-
-def test_queries_as_a_kernel_opt_in(monkeypatch):
-    """The opt-in queries-in-TMEM kernel (DAB_USE_QA=1, read once per process) must rank exactly too.
-    Runs in a subprocess so that the environment switch is seen by a fresh library instance."""
-    import os
-    import subprocess
-    import sys
-    code = r'''
-import sys, os
-root = os.getcwd()
-sys.path.insert(0, root); sys.path.insert(0, os.path.join(root, "django-assistant-bot_b200"))
-import torch
-from dab_b200 import ops
-from oracle import search_ref
-g = torch.Generator().manual_seed(3)
-N, D, Q, k = 60_000, 768, 256, 20
-rows = torch.randn(N, D, generator=g); q = torch.randn(Q, D, generator=g)
-st = ops.ChunkStore(N, D, torch.bfloat16, "cuda:0"); st.set_path("tcgen05"); st.append(rows.cuda())
-assert st.describe_plan(Q, k)["path"] == "tcgen05-qa", st.describe_plan(Q, k)
-s, i = st.search(q.cuda(), k)
-S = search_ref.exact_scores(rows.to(torch.bfloat16).float().numpy(), q.numpy())
-for j in range(Q):
-    search_ref.check_topk_parity(S[j], i[j].cpu().numpy(), s[j].cpu().numpy(), k)
-print("qa ok")
-'''
-    env = dict(os.environ, DAB_USE_QA="1")
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0 and "qa ok" in out.stdout, out.stdout[-1500:] + out.stderr[-1500:]

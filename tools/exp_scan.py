@@ -7,6 +7,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "django-assistant-bot_b200"))
+sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
@@ -41,15 +42,20 @@ def main():
     for _ in range(3):
         st.search_async(q, a.k)
     torch.cuda.synchronize()
+    from bench import ClockSampler
+    cs = ClockSampler(0)
     st.set_profile(True)
     st.get_profile()
+    cs.start()
     for _ in range(a.reps):
         st.search_async(q, a.k)
     torch.cuda.synchronize()
+    clocks = cs.stop()
     p = st.get_profile()
     plan = st.describe_plan(a.q, a.k)
     print(f"lib={os.path.basename(_lib.LIB_PATH)} path={plan.get('path')} scan_ms/search={p['scan_ms'] / a.reps:.3f} "
-          f"search_ms={p['search_ms'] / a.reps:.3f} launches/search={p['scan_launches'] / a.reps:.1f}", flush=True)
+          f"search_ms={p['search_ms'] / a.reps:.3f} launches/search={p['scan_launches'] / a.reps:.1f} sm_mhz={clocks.get('sm_mhz')} "
+          f"reasons={clocks.get('reasons')}", flush=True)
 
 
 if __name__ == "__main__":
