@@ -9,11 +9,11 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompil
 mkdir -p obj
 pids=()
 objs=()
-for f in pool.cu select.cu scan_simt.cu scan_umma.cu scan_umma_quad.cu store.cu noalloc.cu exchange.cu docagg.cu; do
+for f in pool.cu select.cu scan_simt.cu scan_umma.cu scan_umma_quad.cu store.cu filter.cu noalloc.cu exchange.cu docagg.cu; do
   [ -f "$f" ] || continue
   o=obj/${f%.cu}.o
   objs+=("$o")
-  if [ ! -f "$o" ] || [ "$f" -nt "$o" ] || [ common.cuh -nt "$o" ] || [ search.cuh -nt "$o" ] || [ umma.cuh -nt "$o" ] || [ ../../include/dab_b200.h -nt "$o" ]; then
+  if [ ! -f "$o" ] || [ "$f" -nt "$o" ] || [ common.cuh -nt "$o" ] || [ search.cuh -nt "$o" ] || [ store.cuh -nt "$o" ] || [ umma.cuh -nt "$o" ] || [ ../../include/dab_b200.h -nt "$o" ]; then
     ( "$NVCC" "${FLAGS[@]}" -c "$f" -o "$o" > "obj/${f%.cu}.log" 2>&1 || { cat "obj/${f%.cu}.log"; exit 1; } ) &
     pids+=($!)
   fi

@@ -16,7 +16,7 @@
 
 #include <cub/device/device_scan.cuh>
 
-#include "search.cuh"
+#include "store.cuh"
 
 namespace dab {
 
@@ -33,50 +33,6 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 int simt_queries_per_pass(int dim, int dtype);
 
 }  // namespace dab
-
-// cudaEvent pairs around the scan launches of a search (only when profiling is switched on)
-struct dab_profile {
-    bool on = false;
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> scan_events;  // per scan launch
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> search_events;  // per search call
-};
-
-struct dab_store {
-    int device = 0;
-    int dim = 0;
-    int dtype = DAB_F32;
-    int64_t capacity = 0;
-    int64_t size = 0;
-    int64_t id_base = 0;
-    bool explicit_ids = false;
-    void *rows = nullptr;
-    float *inv_norm = nullptr;
-    int64_t *ids = nullptr;
-    void *scratch_base = nullptr;
-    dab::SearchScratch scratch{};
-    int num_sms = 148;
-    int spare_rounds = 0;
-    int path = 0;
-    dab_profile prof;
-    // Per-call verdicts: search number `seq` owns slot seq % kVerdictSlots of both rings; its finish kernels write
-    // {incomplete, inexact} there (HBM ring for the exchange kernel, pinned ring for dab_store_search_status).
-    int *verdict_ring_dev = nullptr;
-    int *verdict_ring_host = nullptr;
-    uint64_t search_seq = 0;
-    // staging of dab_store_search_host (allocated on first use): pinned host + device buffers for one
-    // chunk of DAB_MAX_QUERY_BATCH queries and their DAB_MAX_K results
-    void *io_host = nullptr;
-    void *io_dev = nullptr;
-    std::mutex io_mu;  // one host-buffer search at a time per store (they share the staging buffers)
-    // Searches on one store share its scratch: the mutex orders their ENQUEUE, this event orders their
-    // EXECUTION when callers use different streams (each search waits for the previous one's last kernel).
-    cudaEvent_t scratch_free = nullptr;
-    // Auto path, few queries: the tensor pass is the faster choice unless the corpus is so dense around the
-    // top-k that the rescoring margin overflows (DAB_E_INEXACT) and the call has to be repeated on the CUDA
-    // cores.  After such a verdict the next `small_simt_credit` small searches go to the CUDA cores directly.
-    int small_simt_credit = 0;
-    std::mutex mu;
-};
 
 namespace dab {
 
@@ -226,6 +182,7 @@ extern "C" DAB_API void dab_store_destroy(dab_store *s) {
     if (s->scratch_free) cudaEventDestroy(s->scratch_free);
     if (s->io_host) cudaFreeHost(s->io_host);
     cudaFree(s->io_dev);
+    for (int c = 0; c < DAB_MAX_COLUMNS; c++) cudaFree(s->columns[c]);
     delete s;
 }
 
@@ -793,6 +750,20 @@ __global__ void compact_scatter_kernel(unsigned char *__restrict__ rows, float *
     }
 }
 
+// filter columns follow the same survivors (one int64 per row)
+__global__ void compact_gather_col_kernel(const int64_t *__restrict__ col, const int *__restrict__ flags, const int *__restrict__ pos,
+                                          int64_t c0, int64_t c1, int64_t *__restrict__ stage) {
+    const int64_t i = c0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < c1 && flags[i]) stage[pos[i] - pos[c0]] = col[i];
+}
+__global__ void compact_scatter_col_kernel(int64_t *__restrict__ col, const int *__restrict__ pos, int64_t c0, int64_t c1,
+                                           const int64_t *__restrict__ stage) {
+    const int64_t d0 = pos[c0];
+    const int64_t cnt = pos[c1] - d0;
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < cnt) col[d0 + j] = stage[j];
+}
+
 __global__ void compact_tail_kernel(float *__restrict__ inv_norm, int64_t *__restrict__ ids, const int *__restrict__ pos, int64_t n,
                                     int64_t id_base, int renumber) {
     const int64_t kept = pos[n];
@@ -858,6 +829,13 @@ extern "C" DAB_API int dab_store_compact(dab_store *s, int64_t *removed_out, voi
         compact_scatter_kernel<<<(unsigned)(4 * s->num_sms), 256, 0, st>>>(rows, s->inv_norm, s->ids, t.pos, c0, c1, row_bytes,
                                                                           t.stage_rows, t.stage_inv, t.stage_ids);
         DAB_LAUNCH_OK();
+        for (int c = 0; c < DAB_MAX_COLUMNS; c++) {
+            if (!s->columns[c]) continue;
+            const unsigned blocks = (unsigned)((c1 - c0 + 255) / 256);
+            compact_gather_col_kernel<<<blocks, 256, 0, st>>>(s->columns[c], t.flags, t.pos, c0, c1, t.stage_ids);
+            compact_scatter_col_kernel<<<blocks, 256, 0, st>>>(s->columns[c], t.pos, c0, c1, t.stage_ids);
+            DAB_LAUNCH_OK();
+        }
     }
     compact_tail_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s->inv_norm, s->ids, t.pos, n, s->id_base, s->explicit_ids ? 0 : 1);
     DAB_LAUNCH_OK();

@@ -42,6 +42,8 @@ SIGNATURES = {
     "dab_store_search_status": (c_int, [c_void_p, c_void_p]),
     "dab_store_set_spare_rounds": (c_int, [c_void_p, c_int]),
     "dab_store_set_path": (c_int, [c_void_p, c_int]),
+    "dab_store_set_column": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int64, c_void_p]),
+    "dab_store_build_allow": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "dab_merge_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "dab_doc_aggregate": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                   c_void_p]),
@@ -59,6 +61,16 @@ SIGNATURES = {
     "dab_store_get_profile": (c_int, [c_void_p, POINTER(ctypes.c_float), POINTER(c_int), POINTER(ctypes.c_float),
                                       POINTER(c_int)]),
 }
+
+DAB_MAX_COLUMNS, DAB_MAX_PREDICATES, DAB_COL_ID = 8, 8, -1
+DAB_OP_EQ, DAB_OP_NE, DAB_OP_LT, DAB_OP_LE, DAB_OP_GT, DAB_OP_GE, DAB_OP_IN, DAB_OP_NOT_IN = range(8)
+
+
+class Predicate(ctypes.Structure):
+    """struct dab_predicate of include/dab_b200.h."""
+    _fields_ = [("column", ctypes.c_int32), ("op", ctypes.c_int32), ("value", c_int64), ("set_dev", c_void_p),
+                ("set_n", c_int64)]
+
 
 _lib = None
 

@@ -79,9 +79,11 @@ def create_app(embedder_models: Optional[Iterable[str]] = None, embedders: Optio
             raise HTTPException(status_code=400, detail="Model is not supported")
         try:
             if BINARY_MEDIA_TYPE in http.headers.get("accept", ""):
+                if not request.texts:      # the JSON path answers {"embeddings": []}; same thing in binary
+                    return Response(content=b"", media_type=BINARY_MEDIA_TYPE, headers={"X-Embedding-Shape": "0,0"})
                 embedder = registry[model]
                 if hasattr(embedder, "embed_tensor"):     # device tensor -> one D2H copy, no Python floats
-                    arr = embedder.embed_tensor(request.texts).float().cpu().numpy() if request.texts else np.zeros((0, 0), "<f4")
+                    arr = embedder.embed_tensor(request.texts).float().cpu().numpy()
                 else:
                     arr = np.asarray(await embedder.embeddings(request.texts), dtype="<f4")
                 arr = np.ascontiguousarray(arr, dtype="<f4").reshape(len(request.texts), -1)

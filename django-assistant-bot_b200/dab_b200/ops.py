@@ -198,6 +198,43 @@ class ChunkStore:
                                          _stream(self.device)))
         return rows, inv, ids
 
+    # -- queryset filters on the device
+    def set_column(self, column: int, values: torch.Tensor, row0: int = 0) -> None:
+        """int64 filter column ``column`` for store rows ``[row0, row0 + len(values))`` (document id, bot id, a
+        status code ...): what the WHERE clauses of the reference's querysets test, kept in HBM beside the rows."""
+        _need_cuda(values, "values")
+        values = values.to(torch.int64).contiguous()
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_set_column(self._h, int(column), values.data_ptr(), int(row0), values.numel(),
+                                             _stream(self.device)))
+
+    def build_allow(self, predicates) -> torch.Tensor:
+        """The allow bitmap of a conjunction of predicates, built by one kernel on the device.
+        ``predicates``: up to 8 tuples ``(column, op, operand)`` - column index or ``_lib.DAB_COL_ID``; ``op`` one of
+        ``_lib.DAB_OP_*``; operand an int, or for IN / NOT_IN an ASCENDING int64 CUDA tensor.  Tombstoned rows are
+        never allowed.  Returns the int32 tensor ``search`` takes as ``allow_bitmap``."""
+        preds = list(predicates)
+        if len(preds) > _lib.DAB_MAX_PREDICATES:
+            raise DabError(_lib.DAB_E_INVALID, "at most 8 predicates per call")
+        arr = (_lib.Predicate * max(1, len(preds)))()
+        keep = []
+        for i, (col, op, operand) in enumerate(preds):
+            arr[i].column, arr[i].op = int(col), int(op)
+            if op in (_lib.DAB_OP_IN, _lib.DAB_OP_NOT_IN):
+                _need_cuda(operand, "IN operand")
+                t = operand.to(torch.int64).contiguous()
+                keep.append(t)
+                arr[i].set_dev, arr[i].set_n, arr[i].value = t.data_ptr() if t.numel() else None, t.numel(), 0
+            else:
+                arr[i].value, arr[i].set_dev, arr[i].set_n = int(operand), None, 0
+        words = (len(self) + 31) // 32
+        bitmap = torch.empty(max(words, 1), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_build_allow(self._h, arr, len(preds), bitmap.data_ptr(), _stream(self.device)))
+        # `keep` (the IN sets) must outlive the kernel: same stream as the caller's next use, so returning is safe
+        bitmap._dab_keep = keep
+        return bitmap
+
     # -- read side
     def search_async(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None,
                      out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, *, path: int = -1, spare_rounds: int = -1):

@@ -86,6 +86,10 @@ class DeviceTable:
         self._cols: Dict[str, np.ndarray] = {}
         self._row_of_pk: Dict[int, int] = {}
         self._doc_dev: Optional[torch.Tensor] = None     # device copy of the document_id column (lazy)
+        # filter columns in HBM (dab_store_set_column): name -> (device column index, rows uploaded so far);
+        # values that are not integers (status strings ...) are dictionary-encoded per column
+        self._dev_cols: Dict[str, List[int]] = {}
+        self._codes: Dict[str, Dict[Any, int]] = {}
         self._deleted: set = set()                        # store rows turned into tombstones
         self.documents: Dict[int, Any] = {}
 
@@ -138,6 +142,8 @@ class DeviceTable:
         if not self._deleted:
             return 0
         live = self.live_mask()
+        for name in list(self._dev_cols):                # every row's values on the device before the rows move
+            self._device_column(name)
         removed = self.store.compact()
         if removed != len(self._deleted) or len(self.store) != int(live.sum()):
             raise DabError(1, f"compaction removed {removed} rows, {len(self._deleted)} were tombstoned")
@@ -151,6 +157,8 @@ class DeviceTable:
         self._deleted = set()
         self._doc_dev = None
         self._cols.clear()
+        for name in self._dev_cols:                      # the HBM columns were compacted with the rows
+            self._dev_cols[name][1] = len(self._pks)
         return removed
 
     def live_mask(self) -> Optional[np.ndarray]:
@@ -170,26 +178,37 @@ class DeviceTable:
             rows, _, _ = self.store.export(r0, min(1 << 18, n - r0))
             blocks.append(rows.view(torch.int16).cpu().numpy() if rows.dtype == torch.bfloat16 else rows.cpu().numpy())
         data = np.concatenate(blocks, 0) if blocks else np.zeros((0, self.dim), np.float32)
-        meta = {f"meta__{k}": np.asarray(v) for k, v in self._meta.items()}
+        meta = {}
+        for k, v in self._meta.items():
+            arr = np.asarray(v)
+            if arr.dtype == object:
+                raise DabError(1, f"filter column {k!r} mixes value types; snapshots hold numbers or strings only")
+            meta[f"meta__{k}"] = arr
+        # texts as one UTF-8 blob + lengths (-1 = NULL): plain arrays only, so loading never unpickles anything
+        enc = [None if t is None else t.encode("utf-8") for t in self._text]
         np.savez(path, rows=data, bf16=np.asarray(self.store.dtype == torch.bfloat16), dim=np.asarray(self.dim),
                  pks=np.asarray(self._pks, dtype=np.int64), docs=np.asarray(self._doc, dtype=np.int64),
                  orders=np.asarray(self._order, dtype=np.int64),
-                 texts=np.asarray(["" if t is None else t for t in self._text], dtype=object),
+                 text_blob=np.frombuffer(b"".join(e for e in enc if e is not None), dtype=np.uint8),
+                 text_len=np.asarray([-1 if e is None else len(e) for e in enc], dtype=np.int64),
                  deleted=np.asarray(sorted(self._deleted), dtype=np.int64), **meta)
 
     @classmethod
     def load(cls, path: str, capacity: Optional[int] = None, device=None) -> "DeviceTable":
-        z = np.load(path, allow_pickle=True)
+        z = np.load(path, allow_pickle=False)
         bf16 = bool(z["bf16"])
         n = z["rows"].shape[0]
         t = cls(max(capacity or n, 1), int(z["dim"]), torch.bfloat16 if bf16 else torch.float32, device)
         meta = {k[len("meta__"):]: z[k] for k in z.files if k.startswith("meta__")}
+        blob, lens = z["text_blob"].tobytes(), z["text_len"]
+        ends = np.cumsum(np.maximum(lens, 0))
+        texts = [None if l < 0 else blob[e - l:e].decode("utf-8") for l, e in zip(lens.tolist(), ends.tolist())]
         for r0 in range(0, n, 1 << 18):
             r1 = min(n, r0 + (1 << 18))
             blk = torch.from_numpy(z["rows"][r0:r1])
             emb = blk.view(torch.bfloat16) if bf16 else blk
-            t.add(z["pks"][r0:r1].tolist(), emb, z["docs"][r0:r1].tolist(), [x or None for x in z["texts"][r0:r1].tolist()],
-                  z["orders"][r0:r1].tolist(), **{k: v[r0:r1] for k, v in meta.items()})
+            t.add(z["pks"][r0:r1].tolist(), emb, z["docs"][r0:r1].tolist(), texts[r0:r1],
+                  z["orders"][r0:r1].tolist(), **{k: v[r0:r1].tolist() for k, v in meta.items()})
         dead = z["deleted"].tolist()
         if dead:
             t.delete([t._pks[r] for r in dead])
@@ -210,13 +229,79 @@ class DeviceTable:
         return self._cols[name]
 
     def bitmap_from_mask(self, mask: np.ndarray) -> torch.Tensor:
+        """Utility for callers that already hold a row mask (not used on the query path)."""
         return ops.pack_allow_bitmap(torch.from_numpy(np.ascontiguousarray(mask, dtype=np.bool_)).to(self.device))
 
+    # -- queryset filters on the device -------------------------------------------------------------
+    _ALIASES = {"id": "pk", "document__id": "document_id", "document": "document_id"}
+
+    def _encode(self, name: str, values) -> np.ndarray:
+        """Column values as int64: integers as they are, anything else through a per-column dictionary."""
+        arr = np.asarray(values)
+        if arr.dtype.kind in "iub":
+            return arr.astype(np.int64)
+        codes = self._codes.setdefault(name, {})
+        return np.asarray([codes.setdefault(v, len(codes)) for v in arr.tolist()], dtype=np.int64)
+
+    def _encode_operand(self, name: str, value) -> Optional[int]:
+        """The int64 a filter value compares as; None = a value this column has never held."""
+        value = getattr(value, "pk", value)              # model instances compare by pk, like the ORM
+        if name in self._codes:
+            return self._codes[name].get(value)
+        return int(value)
+
+    def _device_column(self, name: str) -> int:
+        """Index of the HBM column behind ``name``, with every row added so far uploaded (incrementally)."""
+        name = self._ALIASES.get(name, name)
+        host = {"pk": self._pks, "document_id": self._doc, "order": self._order}.get(name, self._meta.get(name))
+        if host is None:
+            raise DabError(1, f"unknown filter column {name!r}; known: pk, document_id, order, {sorted(self._meta)}")
+        if name not in self._dev_cols:
+            if len(self._dev_cols) >= ops._lib.DAB_MAX_COLUMNS:
+                raise DabError(1, f"more than {ops._lib.DAB_MAX_COLUMNS} filter columns in use")
+            self._dev_cols[name] = [len(self._dev_cols), 0]
+        idx, done = self._dev_cols[name]
+        n = len(self)
+        if done < n:
+            vals = torch.from_numpy(self._encode(name, host[done:n])).to(self.device)
+            self.store.set_column(idx, vals, done)
+            self._dev_cols[name][1] = n
+        return idx
+
+    _OPS = {"exact": 0, "lt": 2, "lte": 3, "gt": 4, "gte": 5, "in": 6}
+    _NEG = {0: 1, 1: 0, 2: 5, 5: 2, 3: 4, 4: 3, 6: 7, 7: 6}
+
+    def predicate(self, name: str, lookup: str, value, negate: bool = False):
+        """``(column, op, operand)`` for ``ChunkStore.build_allow`` from a Django-style lookup."""
+        name = self._ALIASES.get(name, name)
+        col = self._device_column(name)
+        op = self._OPS[lookup]
+        coded = name in self._codes
+        if coded and lookup not in ("exact", "in"):
+            raise DabError(1, f"column {name!r} is not numeric: only exact / in lookups apply")
+        if lookup == "in":
+            vals = [self._encode_operand(name, v) for v in value]
+            operand = torch.as_tensor(sorted(v for v in vals if v is not None), dtype=torch.int64).to(self.device)
+        else:
+            operand = self._encode_operand(name, value)
+            if operand is None:                          # a value the column never held: matches nothing
+                op, operand = 6, torch.zeros(0, dtype=torch.int64, device=self.device)
+        return (col, self._NEG[op] if negate else op, operand)
+
+    def build_bitmap(self, predicates) -> torch.Tensor:
+        """AND of the predicates (and of "row is alive"), evaluated on the device; more than 8 predicates are
+        built in groups and combined with a bitwise AND."""
+        preds = list(predicates)
+        step = ops._lib.DAB_MAX_PREDICATES
+        bitmap = self.store.build_allow(preds[:step])
+        for i in range(step, len(preds), step):
+            bitmap = bitmap & self.store.build_allow(preds[i:i + step])
+        return bitmap
+
     def bitmap_from_pks(self, pks: Iterable[int]) -> torch.Tensor:
-        mask = np.zeros(len(self), dtype=np.bool_)
-        rows = [self._row_of_pk[int(p)] for p in pks if int(p) in self._row_of_pk]
-        mask[rows] = True
-        return self.bitmap_from_mask(mask)
+        """The queryset as a pk list (what a Django QuerySet can give us): ``pk IN (sorted pks)`` on the device."""
+        arr = np.unique(np.fromiter((int(p) for p in pks), dtype=np.int64))
+        return self.build_bitmap([(self._device_column("pk"), 6, torch.from_numpy(arr).to(self.device))])
 
     def search_rows(self, query_embeddings, n: int, bitmap: Optional[torch.Tensor] = None):
         """(distances [Q, n'] float64 ascending, store rows [Q, n'] int64); n' <= n."""
@@ -227,7 +312,10 @@ class DeviceTable:
             raise DabError(3, f"different vector dimensions {q.shape[-1]} and {self.dim}")
         if len(self) == 0 or n <= 0:
             return np.zeros((q.shape[0], 0)), np.zeros((q.shape[0], 0), dtype=np.int64)
-        k = min(int(n), ops._lib.DAB_MAX_K)
+        if int(n) > ops._lib.DAB_MAX_K:
+            raise DabError(ops._lib.DAB_E_CAPACITY, f"n = {n} exceeds DAB_MAX_K = {ops._lib.DAB_MAX_K} rows per search "
+                           "(the reference's largest n is 250)")
+        k = int(n)
         scores, ids = self.store.search_host(q, k, bitmap)      # one C call: H2D, search, D2H, verdict, retries
         return 1.0 - scores.astype(np.float64), ids
 
@@ -242,7 +330,9 @@ class DeviceTable:
             return []
         if self._doc_dev is None or self._doc_dev.numel() != len(self):
             self._doc_dev = torch.as_tensor(np.asarray(self._doc, dtype=np.int64)).to(self.device)
-        k = min(int(n), ops._lib.DAB_MAX_K)
+        if int(n) > ops._lib.DAB_MAX_K:
+            raise DabError(ops._lib.DAB_E_CAPACITY, f"max_scores_n * top_n * 10 = {n} exceeds DAB_MAX_K = {ops._lib.DAB_MAX_K}")
+        k = int(n)
         scores, rows = self.store.search(q.to(self.device), k, bitmap)
         docs, dscores = ops.doc_aggregate(scores, rows, self._doc_dev, max_scores_n, top_n)
         docs, dscores = docs[0].cpu().tolist(), dscores[0].cpu().tolist()
@@ -260,10 +350,7 @@ class DeviceTable:
         self.store.close()
 
 
-_LOOKUPS = {
-    "exact": lambda c, v: c == v, "in": lambda c, v: np.isin(c, np.asarray(list(v))),
-    "lt": lambda c, v: c < v, "lte": lambda c, v: c <= v, "gt": lambda c, v: c > v, "gte": lambda c, v: c >= v,
-}
+_LOOKUPS = ("exact", "in", "lt", "lte", "gt", "gte")
 
 
 class ChunkQuerySet:
@@ -271,29 +358,29 @@ class ChunkQuerySet:
     callers use before handing ``qs`` to the search (``.filter(...)`` with equality, ``__in`` and
     comparison lookups; e.g. ``Question.objects.filter(document__wiki__bot=bot, ...)`` in
     assistant/bot/services/context_service/steps/embeddings.py:26-29 and
-    ``filter(document__id__lt=...)`` in assistant/processing/documents/steps/questions.py:124)."""
+    ``filter(document__id__lt=...)`` in assistant/processing/documents/steps/questions.py:124).
 
-    def __init__(self, table: DeviceTable, mask: Optional[np.ndarray] = None):
+    A queryset is a list of predicates; nothing is evaluated until the search needs the allow bitmap,
+    and then ONE kernel evaluates them for every row on the device (``dab_store_build_allow``) - no
+    per-row work on the host, whatever the size of the table."""
+
+    def __init__(self, table: DeviceTable, predicates: Optional[list] = None):
         self.table = table
-        self._mask = mask
+        self._preds = list(predicates or [])       # (column name, lookup, value, negate)
 
     def _apply(self, kwargs, negate: bool) -> "ChunkQuerySet":
-        if self._mask is not None:
-            mask = self._mask.copy()
-        else:
-            live = self.table.live_mask() if hasattr(self.table, "live_mask") else None
-            mask = np.ones(len(self.table), dtype=np.bool_) if live is None else live
+        preds = list(self._preds)
         for key, value in kwargs.items():
             name, op = key, "exact"
             if "__" in key and key.rsplit("__", 1)[1] in _LOOKUPS:
                 name, op = key.rsplit("__", 1)
-            value = getattr(value, "pk", value)  # model instances compare by pk, like the ORM
-            hit = _LOOKUPS[op](self.table.column(name), value)
-            mask &= ~hit if negate else hit
-        return ChunkQuerySet(self.table, mask)
+            if op == "in":
+                value = list(value)
+            preds.append((name, op, value, negate))
+        return ChunkQuerySet(self.table, preds)
 
     def filter(self, **kwargs) -> "ChunkQuerySet":
-        return self._apply(kwargs, False) if kwargs else ChunkQuerySet(self.table, self._mask)
+        return self._apply(kwargs, False)
 
     def exclude(self, **kwargs) -> "ChunkQuerySet":
         return self._apply(kwargs, True)
@@ -301,13 +388,19 @@ class ChunkQuerySet:
     def all(self) -> "ChunkQuerySet":
         return self
 
-    def count(self) -> int:
-        if self._mask is not None:
-            return int(self._mask.sum())
-        return len(self.table) - len(getattr(self.table, "_deleted", ()))
-
     def allow_bitmap(self) -> Optional[torch.Tensor]:
-        return None if self._mask is None else self.table.bitmap_from_mask(self._mask)
+        """None = every (live) row; else the device bitmap of the conjunction."""
+        if not self._preds:
+            return None            # tombstones are skipped by the scan itself
+        return self.table.build_bitmap([self.table.predicate(n, op, v, neg) for n, op, v, neg in self._preds])
+
+    def count(self) -> int:
+        if not self._preds:
+            return len(self.table) - len(getattr(self.table, "_deleted", ()))
+        bm = self.allow_bitmap()
+        n = len(self.table)
+        bits = (bm.view(torch.uint8)[:, None] >> torch.arange(8, device=bm.device, dtype=torch.uint8)[None, :]) & 1
+        return int(bits.reshape(-1)[:n].sum().item())
 
 
 # --------------------------------------------------------------------------- registry / configuration
@@ -448,7 +541,10 @@ async def embedding_search(query: str, qs, max_scores_n: int = 10, top_n: int = 
 
 
 async def get_embedding(text: str) -> List[float]:
-    """search_service.py:155-158."""
-    if _embedder is None:
-        raise DabError(1, "no embedder configured: call dab_b200.search_service.configure(embedder=...)")
-    return (await _embedder.embeddings([text]))[0]
+    """search_service.py:155-158: ``get_ai_embdedder(settings.EMBEDDING_AI_MODEL)`` unless an embedder
+    was set with ``configure``."""
+    embedder = _embedder
+    if embedder is None:
+        from .embedders import get_ai_embdedder
+        embedder = get_ai_embdedder()
+    return (await embedder.embeddings([text]))[0]

@@ -55,6 +55,19 @@ typedef struct dab_store dab_store;
                              * exactly those queries come back poisoned (score NaN, id -1), every other query of the
                              * call is final; repeat the poisoned ones with dab_store_set_path(s, 1) */
 
+/* queryset filters evaluated on the device (dab_store_set_column / dab_store_build_allow) */
+#define DAB_MAX_COLUMNS 8        /* int64 filter columns per store */
+#define DAB_MAX_PREDICATES 8     /* predicates AND-ed in one dab_store_build_allow call */
+#define DAB_COL_ID (-1)          /* pseudo-column: the row id (Django pk) */
+#define DAB_OP_EQ 0
+#define DAB_OP_NE 1
+#define DAB_OP_LT 2
+#define DAB_OP_LE 3
+#define DAB_OP_GT 4
+#define DAB_OP_GE 5
+#define DAB_OP_IN 6              /* value in set_dev[0..set_n), an ASCENDING device array */
+#define DAB_OP_NOT_IN 7
+
 /* limits */
 #define DAB_MAX_K 2048           /* largest n of a search; the reference uses 1, 5, 10, 250 */
 #define DAB_MAX_QUERY_BATCH 256  /* queries scored per corpus pass; larger Q is chunked */
@@ -187,6 +200,31 @@ DAB_API int dab_store_set_spare_rounds(dab_store *s, int rounds);
  * path whenever the row layout allows it, for any number of queries; after a DAB_E_INEXACT verdict on a search
  * of <= 4 queries the next 64 such searches use the CUDA cores directly. */
 DAB_API int dab_store_set_path(dab_store *s, int path);
+
+/*
+ * Queryset filters on the device.  Every reference call searches a FILTERED queryset:
+ *   Question.objects.filter(document__wiki__bot=bot, document__processing__status=COMPLETED)
+ *       assistant/bot/services/context_service/steps/embeddings.py:26-29
+ *   Question.objects.filter(document__id__lt=document.id, ...)
+ *       assistant/processing/documents/steps/questions.py:124
+ * PostgreSQL evaluates those WHERE clauses per row inside the scan; here the columns they test live in HBM
+ * next to the rows (one int64 per row and column: document id, bot id, status code, ...) and ONE kernel turns a
+ * conjunction of predicates into the allow bitmap dab_store_search takes - nothing per row happens on the host.
+ *   dab_store_set_column  values_dev [n] int64 for store rows [row0, row0+n); columns are allocated on first use
+ *                         (capacity * 8 bytes each), follow dab_store_compact, and read 0 where never set
+ *   dab_store_build_allow bitmap_out_dev [ceil(size/32)] uint32: bit r = row r is alive (not a tombstone) AND
+ *                         passes all n_pred predicates (n_pred = 0: alive rows).  A queryset given as a list of
+ *                         pks is the predicate {DAB_COL_ID, DAB_OP_IN, sorted pks}.
+ */
+typedef struct dab_predicate {
+    int32_t column;          /* 0..DAB_MAX_COLUMNS-1 or DAB_COL_ID */
+    int32_t op;              /* DAB_OP_* */
+    int64_t value;           /* operand of the comparison ops */
+    const int64_t *set_dev;  /* DAB_OP_IN / DAB_OP_NOT_IN: ascending int64 device array */
+    int64_t set_n;
+} dab_predicate;
+DAB_API int dab_store_set_column(dab_store *s, int column, const int64_t *values_dev, int64_t row0, int64_t n, void *stream);
+DAB_API int dab_store_build_allow(dab_store *s, const dab_predicate *preds, int n_pred, uint32_t *bitmap_out_dev, void *stream);
 
 /*
  * k-way merge of per-shard top-k lists (after the all-gather).  New in the build: the

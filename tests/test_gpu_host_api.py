@@ -155,6 +155,43 @@ def test_b200_embedder_matches_reference_embedder(golden_dir):
     assert asyncio.run(emb.embeddings([])) == []
 
 
+def test_embedder_truncation_bf16_forward_and_embed_into():
+    """(f)3: over-long texts are truncated instead of failing; a bf16 encoder feeds the pool kernel's bf16 input
+    path; embed_into appends the pooled rows to a store without leaving the device
+    (assistant/processing/documents/steps/embeddings.py:27-39)."""
+    from dab_b200 import ops
+    from dab_b200.embedders import B200TransformersEmbedder
+    from oracle import pool_ref
+    model, tok, texts = _golden_model_and_tokenizer()
+    full = B200TransformersEmbedder("m", model=model, tokenizer=tok, device=DEV)
+    cut = B200TransformersEmbedder("m", model=model, tokenizer=tok, device=DEV, max_length=16)
+    e_full = np.asarray(asyncio.run(full.embeddings(texts)))
+    e_cut = np.asarray(asyncio.run(cut.embeddings(texts)))
+    enc = tok(texts)
+    ids, mask = enc["input_ids"][:, :16].to(DEV), enc["attention_mask"][:, :16].to(DEV)
+    with torch.no_grad():
+        hidden = model.to(DEV)(input_ids=ids, attention_mask=mask).last_hidden_state
+    want, _ = pool_ref.masked_mean_pool(hidden.cpu().numpy(), mask.cpu().numpy())
+    np.testing.assert_allclose(e_cut, want, rtol=1e-4, atol=5e-6)
+    short = [i for i, t in enumerate(texts) if int(enc["attention_mask"][i].sum()) <= 16]
+    np.testing.assert_allclose(e_cut[short], e_full[short], rtol=1e-4, atol=5e-6)      # short texts are untouched
+    # bf16 forward: same direction within bf16 noise, still unit norm
+    import copy
+    b16 = B200TransformersEmbedder("m", model=copy.deepcopy(model), tokenizer=tok, device=DEV, dtype=torch.bfloat16)
+    hidden16, _ = b16._encode_batch(texts)
+    assert hidden16.dtype == torch.bfloat16
+    e16 = np.asarray(asyncio.run(b16.embeddings(texts)))
+    np.testing.assert_allclose(np.linalg.norm(e16, axis=1), 1.0, rtol=1e-5)
+    assert ((e16 * e_full).sum(axis=1) > 0.995).all()
+    # ingest: encode -> pool -> append, on the device, into an fp32 and a bf16 store
+    for dtype in (torch.float32, torch.bfloat16):
+        store = ops.ChunkStore(64, 384, dtype, DEV)
+        assert full.embed_into(store, texts) == len(texts) and len(store) == len(texts)
+        s, i = store.search(torch.from_numpy(e_full[2:3]).float().to(DEV), 2)
+        assert i[0, 0].item() == 2 and abs(s[0, 0].item() - 1.0) < (1e-5 if dtype == torch.float32 else 4e-3)
+        store.close()
+
+
 def test_endpoint_with_b200_embedder():
     from fastapi.testclient import TestClient
     from dab_b200.embedders import B200TransformersEmbedder

@@ -37,27 +37,22 @@ def test_cosine_helpers_match_reference_golden(golden_dir):
 
 
 class _FakeTable:
-    def __init__(self, n):
-        self.cols = {"pk": np.arange(n), "document_id": np.arange(n) // 3, "document__wiki__bot": np.arange(n) % 2}
-
     def __len__(self):
-        return len(self.cols["pk"])
-
-    def column(self, name):
-        return self.cols[{"document__id": "document_id", "id": "pk"}.get(name, name)]
+        return 30
 
 
-def test_chunk_queryset_filter_lookups():
+def test_chunk_queryset_collects_predicates_lazily():
+    """filter / exclude only record Django-style lookups (nothing is evaluated on the host: the device builds the
+    bitmap when the search asks for it, tests/test_gpu_filters.py); each call returns a new view."""
     from dab_b200.search_service import ChunkQuerySet
-    qs = ChunkQuerySet(_FakeTable(30))
-    assert qs.count() == 30 and qs._mask is None
+    qs = ChunkQuerySet(_FakeTable())
+    assert qs.count() == 30 and qs.allow_bitmap() is None
     a = qs.filter(document__wiki__bot=1)
-    assert a.count() == 15 and qs.count() == 30                      # filter returns a new view
-    b = a.filter(document__id__lt=4)
-    assert set(np.nonzero(b._mask)[0]) == {1, 3, 5, 7, 9, 11}
-    assert qs.filter(pk__in=[2, 4, 99]).count() == 2
-    assert qs.exclude(document_id=0).count() == 27
-    assert qs.filter(document_id__gte=9).count() == 3
+    b = a.filter(document__id__lt=4).exclude(pk__in=(2, 4, 99))
+    assert qs._preds == [] and a._preds == [("document__wiki__bot", "exact", 1, False)]
+    assert b._preds == [("document__wiki__bot", "exact", 1, False), ("document__id", "lt", 4, False),
+                        ("pk", "in", [2, 4, 99], True)]
+    assert qs.all() is qs
 
 
 class _GoodEmbedder:
@@ -118,11 +113,75 @@ def test_endpoint_skips_models_that_fail_to_load():
         assert c.post("/embeddings/", json={"model": "broken", "texts": ["a"]}).status_code == 400
 
 
-def test_get_embedding_requires_configuration():
+def test_get_embedding_requires_configuration(monkeypatch):
     from dab_b200 import DabError, search_service
     search_service.configure(None)
-    with pytest.raises(DabError, match="no embedder configured"):
+    monkeypatch.delenv("EMBEDDING_AI_MODEL", raising=False)
+    with pytest.raises(DabError, match="no embedding model named"):
         asyncio.run(search_service.get_embedding("x"))
     search_service.configure(_GoodEmbedder())
     assert asyncio.run(search_service.get_embedding("abc")) == [3.0, 1.0]
     search_service.configure(None)
+
+
+def _serve(app):
+    """The FastAPI app on a real socket (uvicorn in a thread), for clients that speak HTTP themselves."""
+    import socket
+    import threading
+    import time
+    import uvicorn
+    sock = socket.socket()
+    sock.bind(("127.0.0.1", 0))
+    port = sock.getsockname()[1]
+    sock.close()
+    server = uvicorn.Server(uvicorn.Config(app, host="127.0.0.1", port=port, log_level="error"))
+    th = threading.Thread(target=server.run, daemon=True)
+    th.start()
+    for _ in range(200):
+        if server.started:
+            break
+        time.sleep(0.05)
+    assert server.started
+    return server, th, f"http://127.0.0.1:{port}"
+
+
+def test_http_clients_and_factory_against_the_endpoint(monkeypatch):
+    """The reference's kept surface end to end over HTTP: ``get_ai_embdedder('gpu_service:<model>')``
+    (assistant/ai/services/ai_service.py:61-67) builds the client, the client talks to this repository's
+    ``POST /embeddings/``.  Where the reference tree is present (the build container) its OWN unmodified
+    ``GPUServiceEmbedder`` is driven against the app as well."""
+    import asyncio
+    import os
+    import sys
+    from dab_b200 import embedders
+    from dab_b200.gpu_service import create_app
+    server, th, url = _serve(create_app(embedders={"some/model": _GoodEmbedder(), "bad": _BadEmbedder()}))
+    try:
+        monkeypatch.setenv("GPU_SERVICE_ENDPOINT", url)
+        monkeypatch.setenv("EMBEDDING_AI_MODEL", "gpu_service:Some/Model")
+        e = embedders.get_ai_embdedder("gpu_service:Some/Model")
+        assert isinstance(e, embedders.GPUServiceEmbedder) and isinstance(e, embedders.AIEmbedder)
+        assert asyncio.run(e.embeddings(["ab", "abcd"])) == [[2.0, 1.0], [4.0, 1.0]]
+        assert asyncio.run(embedders.GPUServiceEmbedder(url, "some/model", binary=True).embeddings(["abc"])) == [[3.0, 1.0]]
+        with pytest.raises(Exception, match="status code 500"):
+            asyncio.run(embedders.get_ai_embdedder("gpu_service:bad").embeddings(["x"]))
+        with pytest.raises(Exception, match="status code 400"):
+            asyncio.run(embedders.get_ai_embdedder("gpu_service:unknown").embeddings(["x"]))
+        with pytest.raises(Exception):
+            embedders.get_ai_embdedder("text-embedding-3-small")
+        # search_service.get_embedding falls back to the factory with settings.EMBEDDING_AI_MODEL (search_service.py:155-158)
+        from dab_b200 import search_service as ss
+        ss.configure(embedder=None)
+        assert asyncio.run(ss.get_embedding("hello")) == [5.0, 1.0]
+        if os.path.isdir("/root/reference"):
+            sys.path.insert(0, "/root/reference")
+            try:
+                from assistant.ai.embedders.gpu_service import GPUServiceEmbedder as RefClient
+                assert asyncio.run(RefClient(base_url=url, model="some/model").embeddings(["ab", "abcd"])) == [[2.0, 1.0], [4.0, 1.0]]
+                with pytest.raises(Exception, match="status code 400"):
+                    asyncio.run(RefClient(base_url=url, model="nope").embeddings(["x"]))
+            finally:
+                sys.path.remove("/root/reference")
+    finally:
+        server.should_exit = True
+        th.join(timeout=5)
