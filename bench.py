@@ -478,13 +478,19 @@ def main():
     env.barrier, env.max_over_ranks = barrier, max_over_ranks
 
     if w["kind"] == "pool":
-        return bench_pool(args, w, rank, world, dev, env.peaks, barrier, max_over_ranks)
+        return bench_pool(args, w, env)
 
     verify = not args.no_verify
     targets = {}
     with_targets = args.workload == DEFAULT_WORKLOAD and not args.no_targets and not args.rows
     # ------------------------------------------------------------------ N=1: the single-GPU configs first
     # configs[1] and configs[2] do not fit beside the 154 GB store of configs[3]: measured and freed before it is built
+    if with_targets:
+        # configs[4] (ingest): pool + append into the owning shard on every rank, no collective
+        m5 = measure_ingest(env, dict(WORKLOADS["c5"]), args.steps, args.warmup)
+        targets["c5"] = dict(desc=WORKLOADS["c5"]["desc"], value=m5["value"], unit="chunks/s", ms_per_step=m5["ms_per_step"],
+                             pool_ms=m5["pool_ms"], e2e=m5["e2e"]["value"], hbm_frac=m5["hbm_frac"], hbm_frac_step=m5["hbm_frac_step"],
+                             verified=m5["verified"], config=m5["config"])
     if with_targets and world == 1:
         for name in ("c2", "c3"):
             sw = dict(WORKLOADS[name])
@@ -558,77 +564,100 @@ def main():
         dist.destroy_process_group()
 
 
-def bench_pool(args, w, rank, world, dev, peaks, barrier, max_over_ranks):
-    import torch
-    import torch.distributed as dist
-    from dab_b200 import _lib, ops
-    L = _lib.lib()
+def measure_ingest(env, w, steps, warmup, cpu_baseline=False):
+    """configs[4] as a PATH, not a kernel: every rank pools + normalises its own batch of encoder hidden states
+    and appends the rows to its own shard of a row-sharded store (chunk -> GPU = row -> shard: no collective).
+    One step = B chunks per GPU; `value` = chunks/s over all ranks (weak scaling)."""
+    torch, dev, rank, world, L = env.torch, env.dev, env.rank, env.world, env.L
+    from dab_b200 import ops, sharded
     B, T, D = w["B"], w["T"], w["dim"]
+    total = w.get("rows", 1_000_000)
+    sh = sharded.ShardedStore(total, D, torch.bfloat16, dev, exchange="nccl")
     g = torch.Generator(device=dev).manual_seed(777 + rank)
-    # several resident batches so that consecutive steps never re-read L2-resident data
-    nb = 4
+    nb = 4                                   # resident batches rotated so that no step re-reads L2-resident data
     hidden = [torch.randn(B, T, D, generator=g, device=dev) for _ in range(nb)]
     lengths = torch.randint(16, T + 1, (B,), generator=torch.Generator().manual_seed(555))
     mask = (torch.arange(T)[None] < lengths[:, None]).to(torch.int64)
     mask_dev = mask.to(dev)
     hidden_host = torch.randn(B, T, D).pin_memory()
     mask_host = mask.pin_memory()
-    out_host = torch.empty(B, D).pin_memory()
+    ack_host = torch.empty(B, dtype=torch.float32).pin_memory()
     it = [0]
+    cap = sh.hi - sh.lo
+
+    def room():
+        if len(sh.local) + B > cap:          # the shard is full: start over (the timed work per step is unchanged)
+            sh.local.reset()
 
     def step_device():
         it[0] += 1
-        return ops.pool_l2norm(hidden[it[0] % nb], mask_dev)
+        room()
+        return sh.ingest(hidden[it[0] % nb], mask_dev)
 
     def step_e2e():
+        # host buffers in (the encoder's output arriving from elsewhere), the rows' inverse norms back as the receipt
         h = hidden_host.to(dev, non_blocking=True)
         m = mask_host.to(dev, non_blocking=True)
-        out_host.copy_(ops.pool_l2norm(h, m), non_blocking=True)
+        room()
+        n0 = len(sh.local)
+        sh.ingest(h, m)
+        _, inv, _ = sh.local.export(n0, B)
+        ack_host.copy_(inv, non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
-    def timed(fn, steps):
-        barrier()
+    def timed(fn, n):
+        env.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(steps):
+        for _ in range(n):
             fn()
         e1.record()
-        barrier()
-        return max_over_ranks(e0.elapsed_time(e1))
+        env.barrier()
+        return env.max_over_ranks(e0.elapsed_time(e1))
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step_device()
-    sampler = ClockSampler(dev.index)
-    if rank == 0:
-        sampler.start()
     l0 = L.dab_launch_count()
-    ms = timed(step_device, args.steps)
+    ms = timed(step_device, steps)
     launches = L.dab_launch_count() - l0
+    # the pool kernel alone, for the roofline (the append adds a pass over B x D bf16 = 0.2 % of the bytes)
+    def pool_only():
+        it[0] += 1
+        return ops.pool_l2norm(hidden[it[0] % nb], mask_dev, want_bf16=True)
+    for _ in range(3):
+        pool_only()
+    ms_pool = timed(pool_only, steps)
     for _ in range(3):
         step_e2e()
-    ms_e2e = timed(step_e2e, max(3, args.steps // 4))
-    e2e_steps = max(3, args.steps // 4)
-    clocks = sampler.stop() if rank == 0 else None
+    e2e_steps = max(3, steps // 4)
+    ms_e2e = timed(step_e2e, e2e_steps)
+    # parity of the path: what landed in the shard is the pooled batch (checked against a torch fp32 statement)
+    sh.local.reset()
+    sh.ingest(hidden[0], mask_dev)
+    rows, inv, ids = sh.local.export(0, B)
+    m = mask_dev.float()
+    want = torch.nn.functional.normalize((hidden[0] * m[:, :, None]).sum(1) / m.sum(1, keepdim=True).clamp(min=1), dim=1)
+    err = float((rows.float() - want).abs().max())
+    assert err < 2 ** -8, f"ingested rows differ from the pooled batch by {err}"      # bf16 rounding of unit-norm rows
+    assert int(ids[0]) == sh.lo and int(ids[-1]) == sh.lo + B - 1
     # the kernel skips masked-out token rows, so the bytes it must move are the unmasked ones
     tokens = int(mask.sum())
-    alg_bytes = tokens * D * 4 + B * T * 8 + B * D * 4
+    alg_bytes = tokens * D * 4 + B * T * 8 + B * D * (4 + 2)
     nominal_bytes = B * (T * D * 4 + T * 8 + D * 4)
-    ach = alg_bytes / (ms / args.steps * 1e-3) / 1e9
-    if rank != 0:
-        return
-    line = dict(metric="ingest pool+L2norm chunks/sec", value=world * B * args.steps / (ms * 1e-3), unit="chunks/s",
-                n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True,
-                scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config={"workload": args.workload, "desc": w["desc"], "B": B, "T": T, "dim": D,
-                        "l2": f"{nb} resident batches of {B * T * D * 4 / 1e6:.0f} MB rotated (> 126 MB L2)"},
-                e2e=dict(value=world * B * e2e_steps / (ms_e2e * 1e-3), unit="chunks/s",
-                         h2d_bytes_per_step=B * T * D * 4 + B * T * 8, d2h_bytes_per_step=B * D * 4),
-                gpu_launches=int(launches), clocks=clocks,
-                roofline=dict(bound="hbm", achieved=ach, peak=peaks["hbm"], unit="GB/s", frac=ach / peaks["hbm"],
-                              traffic=None, kernel="pool_l2norm_kernel", peak_source=peaks["source"],
-                              note=f"algorithmic bytes count only unmasked token rows ({tokens} of {B * T}); "
-                                   f"with every row counted: {nominal_bytes / (ms / args.steps * 1e-3) / 1e9:.0f} GB/s"))
-    if world == 1 and not args.no_cpu_baseline:
+    ach = alg_bytes / (ms_pool / steps * 1e-3) / 1e9
+    out = dict(value=world * B * steps / (ms * 1e-3), unit="chunks/s", ms_per_step=ms / steps, pool_ms=ms_pool / steps,
+               e2e=dict(value=world * B * e2e_steps / (ms_e2e * 1e-3), unit="chunks/s",
+                        h2d_bytes_per_step=B * T * D * 4 + B * T * 8, d2h_bytes_per_step=B * 4, ms_per_step=ms_e2e / e2e_steps),
+               launches=int(launches), hbm_frac=ach / env.peaks["hbm"],
+               hbm_frac_step=alg_bytes / (ms / steps * 1e-3) / 1e9 / env.peaks["hbm"],
+               roofline=dict(bound="hbm", achieved=ach, peak=env.peaks["hbm"], unit="GB/s", frac=ach / env.peaks["hbm"],
+                             traffic=None, kernel="pool_l2norm_kernel", peak_source=env.peaks["source"],
+                             note=f"algorithmic bytes count only unmasked token rows ({tokens} of {B * T}); with every row "
+                                  f"counted: {nominal_bytes / (ms_pool / steps * 1e-3) / 1e9:.0f} GB/s"),
+               verified=f"rows landed in shard rows [{sh.lo}, {sh.lo + B}) equal the pooled batch (max abs diff {err:.1e} after bf16 rounding)",
+               config={"B": B, "T": T, "dim": D, "store": f"{total} x {D} bf16 row-sharded over {world} GPU(s)",
+                       "l2": f"{nb} resident batches of {B * T * D * 4 / 1e6:.0f} MB rotated (> 126 MB L2)"})
+    if cpu_baseline and rank == 0:
         from oracle import pool_ref
         hs, msk = hidden_host[:32], mask[:32]
         t0 = time.perf_counter()
@@ -637,10 +666,34 @@ def bench_pool(args, w, rank, world, dev, peaks, barrier, max_over_ranks):
             pool_ref.masked_mean_pool_torch_cpu(hs, msk)
             reps += 1
         dt = (time.perf_counter() - t0) / reps
-        line["cpu_baseline"] = dict(value=32 / dt, unit="chunks/s", cores=torch.get_num_threads(), kind="port",
-                                    sample=f"{reps} reps of 32 chunks, CPU torch masked mean + F.normalize")
+        out["cpu_baseline"] = dict(value=32 / dt, unit="chunks/s", cores=torch.get_num_threads(), kind="port",
+                                   sample=f"{reps} reps of 32 chunks, CPU torch masked mean + F.normalize")
+    sh.close()
+    del hidden
+    torch.cuda.empty_cache()
+    return out
+
+
+def bench_pool(args, w, env):
+    import torch.distributed as dist
+    sampler = ClockSampler(env.dev.index)
+    if env.rank == 0:
+        sampler.start()
+    m = measure_ingest(env, w, args.steps, args.warmup, cpu_baseline=(env.world == 1 and not args.no_cpu_baseline))
+    clocks = sampler.stop() if env.rank == 0 else None
+    if env.rank != 0:
+        if env.world > 1:
+            dist.destroy_process_group()
+        return
+    line = dict(metric="ingest pool+L2norm chunks/sec", value=m["value"], unit="chunks/s", n_gpus=env.world, steps=args.steps,
+                warmup=args.warmup, ms_per_step=m["ms_per_step"], higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="f32", data="synthetic", config=dict(m["config"], workload=args.workload, desc=w["desc"]),
+                e2e=m["e2e"], gpu_launches=m["launches"], clocks=clocks, roofline=m["roofline"], verified=m["verified"],
+                pool_ms=m["pool_ms"])
+    if "cpu_baseline" in m:
+        line["cpu_baseline"] = m["cpu_baseline"]
     print(json.dumps(line))
-    if world > 1:
+    if env.world > 1:
         dist.destroy_process_group()
 
 

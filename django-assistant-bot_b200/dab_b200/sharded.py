@@ -175,6 +175,21 @@ class ShardedStore:
         """Rows of THIS shard, in global row order."""
         self.local.append(rows)
 
+    def ingest(self, hidden: torch.Tensor, mask: Optional[torch.Tensor] = None, ids: Optional[torch.Tensor] = None) -> int:
+        """The write side of the sharded store, data-parallel and without any collective: this rank pools and
+        normalises the encoder output of ITS chunks (``dab_pool_l2norm``) and appends the rows to its own shard -
+        the chunk -> GPU map is the row -> shard map (``shard_bounds``), so an embedding is born on the GPU that
+        will scan it.  What ``embedder.embeddings(texts)`` + ``bulk_update(['embedding'])`` do through the
+        embedding service and PostgreSQL (assistant/processing/documents/steps/embeddings.py:27-39,57-69).
+        ``hidden`` [B,T,D] fp32/bf16 on this rank's device, ``mask`` [B,T].  Returns the rows appended."""
+        from . import ops
+        if self.local.dtype == torch.bfloat16:
+            _, rows = ops.pool_l2norm(hidden, mask, want_bf16=True)      # the kernel's bf16 output is what the store holds
+        else:
+            rows = ops.pool_l2norm(hidden, mask)
+        self.local.append(rows, ids)
+        return int(rows.shape[0])
+
     def _search_p2p(self, queries: torch.Tensor, k: int, allow_bitmap):
         from ._lib import DabError, lib
         if queries.dim() == 1:

@@ -64,3 +64,25 @@ def test_pool_argument_errors():
         _run(torch.zeros(1, 2, 6), None)
     with pytest.raises(DabError, match="mask shape"):
         _run(torch.zeros(1, 2, 8), torch.ones(1, 3, dtype=torch.int64))
+
+
+def test_ingest_pools_and_appends_into_the_owning_shard():
+    """The write path as a path (assistant/processing/documents/steps/embeddings.py:27-39): hidden states in,
+    rows in the shard out - pool, normalise, append, on the device; then the rows are searchable."""
+    from dab_b200 import sharded
+    g = torch.Generator().manual_seed(11)
+    B, T, D = 48, 40, 256
+    hidden = torch.randn(B, T, D, generator=g)
+    lengths = torch.randint(1, T + 1, (B,), generator=g)
+    mask = (torch.arange(T)[None] < lengths[:, None]).to(torch.int64)
+    want, _ = pool_ref.masked_mean_pool(hidden.numpy(), mask.numpy())
+    for dtype, tol in ((torch.float32, 2e-6), (torch.bfloat16, 2 ** -8)):
+        sh = sharded.ShardedStore(1000, D, dtype, DEV)            # world size 1: this rank owns rows [0, 1000)
+        assert sh.ingest(hidden[:20].to(DEV), mask[:20].to(DEV)) == 20
+        assert sh.ingest(hidden[20:].to(DEV), mask[20:].to(DEV)) == B - 20 and len(sh.local) == B
+        rows, inv, ids = sh.local.export(0, B)
+        np.testing.assert_allclose(rows.float().cpu().numpy(), want, rtol=0, atol=tol)
+        assert ids.cpu().tolist() == list(range(B))
+        s, i = sh.search(torch.from_numpy(want[5:6]).to(DEV), 1)
+        assert i[0, 0].item() == 5 and abs(s[0, 0].item() - 1.0) < 1e-3
+        sh.close()
