@@ -8,6 +8,7 @@ import torch
 from oracle import pool_ref
 
 pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
 
 
 def _run(hidden, mask, **kw):
