@@ -9,7 +9,7 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompil
 mkdir -p obj
 pids=()
 objs=()
-for f in pool.cu select.cu scan_simt.cu scan_umma.cu scan_umma_quad.cu store.cu filter.cu noalloc.cu exchange.cu docagg.cu; do
+for f in pool.cu select.cu scan_simt.cu scan_umma.cu scan_umma_quad.cu store.cu filter.cu noalloc.cu exchange.cu sharded.cu docagg.cu; do
   [ -f "$f" ] || continue
   o=obj/${f%.cu}.o
   objs+=("$o")

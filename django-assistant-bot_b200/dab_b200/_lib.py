@@ -52,6 +52,11 @@ SIGNATURES = {
     "dab_store_status_dev": (c_void_p, [c_void_p]),
     "dab_exchange_merge_topk": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, ctypes.c_uint32, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dab_sharded_create": (c_int, [POINTER(c_void_p), POINTER(c_int), c_int, c_int64, c_int, c_int, c_int, c_int]),
+    "dab_sharded_destroy": (None, [c_void_p]),
+    "dab_sharded_num_shards": (c_int, [c_void_p]),
+    "dab_sharded_shard": (c_void_p, [c_void_p, c_int, POINTER(c_int), POINTER(c_int64), POINTER(c_int64), POINTER(c_void_p)]),
+    "dab_sharded_search_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "dab_search_noalloc": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p,
                                    c_void_p, c_void_p, c_void_p]),
     "dab_store_describe_plan": (c_int, [c_void_p, c_int, c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int),

@@ -103,10 +103,23 @@ class ChunkStore:
         if id_base:
             check(lib().dab_store_set_id_base(self._h, int(id_base)))
 
+    @classmethod
+    def _view(cls, handle: int, device: torch.device, dim: int, dtype: torch.dtype) -> "ChunkStore":
+        """A non-owning wrapper around a dab_store that something else created and will destroy
+        (the shards of ``dab_sharded_create``)."""
+        self = cls.__new__(cls)
+        self.device, self.dim, self.dtype = device, int(dim), dtype
+        self._h = _lib.c_void_p(handle)
+        self._path = 0
+        self._lock = threading.Lock()
+        self._borrowed = True
+        return self
+
     # -- lifecycle
     def close(self) -> None:
         if getattr(self, "_h", None) is not None and self._h.value:
-            lib().dab_store_destroy(self._h)
+            if not getattr(self, "_borrowed", False):
+                lib().dab_store_destroy(self._h)
             self._h = _lib.c_void_p()
 
     def __del__(self):  # pragma: no cover

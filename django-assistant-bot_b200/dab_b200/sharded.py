@@ -20,7 +20,7 @@ Two transports for the exchange:
 from __future__ import annotations
 
 import ctypes
-from typing import Optional, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
@@ -272,3 +272,76 @@ class ShardedStore:
 
     def close(self) -> None:
         self.local.close()
+
+
+class LocalShardedStore:
+    """The row-sharded store driven by ONE process (``dab_sharded_*``): what a Django / Celery / FastAPI worker can
+    use without ``torchrun`` - the reference searches from an asgiref worker thread of an ordinary web process
+    (assistant/rag/services/search_service.py:191).  ``devices`` lists the GPU of every shard; rows
+    ``[g*N/G, (g+1)*N/G)`` live on ``devices[g]`` with ids = global row index.  ``search_host`` takes host queries
+    (NumPy / list) and returns NumPy ``(scores [Q,k], ids [Q,k])``: the shards scan concurrently, the library's own
+    exchange kernel merges over NVLink peer memory, one copy brings the answer back."""
+
+    def __init__(self, total_rows: int, dim: int, dtype: torch.dtype = torch.bfloat16, devices: Optional[Sequence[int]] = None,
+                 max_q: int = 256, max_k: int = 256):
+        from . import _lib, ops
+        from ._lib import check, lib
+        if devices is None:
+            devices = list(range(torch.cuda.device_count()))
+        self.devices = [int(d) for d in devices]
+        self.total_rows, self.dim, self.dtype = int(total_rows), int(dim), dtype
+        self._h = ctypes.c_void_p()
+        arr = (ctypes.c_int * len(self.devices))(*self.devices)
+        check(lib().dab_sharded_create(ctypes.byref(self._h), arr, len(self.devices), self.total_rows, self.dim,
+                                       ops._DTYPES[dtype], int(max_q), int(max_k)))
+        self.shards = []
+        self.bounds = []
+        self.streams = []
+        for g in range(len(self.devices)):
+            dev, lo, hi, st = ctypes.c_int(), ctypes.c_int64(), ctypes.c_int64(), ctypes.c_void_p()
+            h = lib().dab_sharded_shard(self._h, g, ctypes.byref(dev), ctypes.byref(lo), ctypes.byref(hi), ctypes.byref(st))
+            self.shards.append(ops.ChunkStore._view(h, torch.device("cuda", dev.value), self.dim, dtype))
+            self.bounds.append((lo.value, hi.value))
+            self.streams.append(st.value)
+
+    def append(self, g: int, rows: torch.Tensor) -> None:
+        """Rows of shard ``g`` in global row order (a tensor on ``devices[g]``)."""
+        self.shards[g].append(rows)
+
+    def ingest(self, g: int, hidden: torch.Tensor, mask: Optional[torch.Tensor] = None) -> int:
+        """Pool + normalise + append on the GPU that owns the rows (see ``ShardedStore.ingest``)."""
+        from . import ops
+        if self.dtype == torch.bfloat16:
+            _, rows = ops.pool_l2norm(hidden, mask, want_bf16=True)
+        else:
+            rows = ops.pool_l2norm(hidden, mask)
+        self.shards[g].append(rows)
+        return int(rows.shape[0])
+
+    def search_host(self, queries, k: int):
+        import numpy as np
+        from ._lib import DabError, check, lib
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        if q.ndim != 2 or q.shape[1] != self.dim:
+            raise DabError(3, f"different vector dimensions {q.shape[-1]} and {self.dim}")
+        Q = q.shape[0]
+        scores = np.empty((Q, k), dtype=np.float32)
+        ids = np.empty((Q, k), dtype=np.int64)
+        check(lib().dab_sharded_search_host(self._h, q.ctypes.data, Q, int(k), scores.ctypes.data, ids.ctypes.data))
+        return scores, ids
+
+    def close(self) -> None:
+        from ._lib import lib
+        if self._h.value:
+            for s in self.shards:
+                s.close()
+            lib().dab_sharded_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass

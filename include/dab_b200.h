@@ -273,6 +273,30 @@ DAB_API int dab_exchange_merge_topk(void *const *peer_bases_dev, int rank, int R
                                     int64_t *out_ids_dev, int *out_status_dev_or_null, void *stream);
 
 /*
+ * The row-sharded store behind ONE process: what a Django / Celery / FastAPI worker can call without a launcher
+ * (the reference searches from an asgiref worker thread, assistant/rag/services/search_service.py:191, and serves
+ * embeddings from gunicorn workers, gpu_service/gunicorn_conf.py:9).  New in the build, like dab_merge_topk: the
+ * reference has one PostgreSQL table.  Shard g lives on devices[g] and holds rows [g*N/G, (g+1)*N/G), ids = global
+ * row index; the handle owns a stream, a peer-mapped staging block (cudaDeviceEnablePeerAccess) and the query /
+ * result staging per device.  A device may be listed more than once (several shards on one GPU; used by tests).
+ *   dab_sharded_shard        the dab_store of shard g (append / set_column / delete through the store API, with
+ *                            device_out current and stream_out or any stream of that device); any output may be NULL
+ *   dab_sharded_search_host  host queries in, merged host results out: every shard scans on its own device and
+ *                            stream, dab_exchange_merge_topk runs on every device, shard 0's merged lists and the
+ *                            OR-ed verdict return in one copy; inexact / incomplete verdicts are retried inside
+ *                            (exact path / spare rounds).  Synchronous; one search at a time per handle.
+ */
+typedef struct dab_sharded dab_sharded;
+DAB_API int dab_sharded_create(dab_sharded **out, const int *devices, int n_devices, int64_t total_rows, int dim, int dtype,
+                               int max_q, int max_k);
+DAB_API void dab_sharded_destroy(dab_sharded *sh);
+DAB_API int dab_sharded_num_shards(const dab_sharded *sh);
+DAB_API dab_store *dab_sharded_shard(dab_sharded *sh, int g, int *device_out, int64_t *row_lo_out, int64_t *row_hi_out,
+                                     void **stream_out);
+DAB_API int dab_sharded_search_host(dab_sharded *sh, const float *q_host, int Q, int k, float *out_scores_host,
+                                    int64_t *out_ids_host);
+
+/*
  * Exact cosine top-k over rows the CALLER owns, without allocating anything.
  * No counterpart in the reference (there the rows live in PostgreSQL and the executor
  * allocates as it pleases); it exists for hosts of this library that cannot call cudaMalloc:
