@@ -388,6 +388,51 @@ class SearchRun:
         out["_res"] = (res_s, res_i)          # the last timed search's answer (dropped before printing)
         return out
 
+    def measure_filtered(self, steps, warmup):
+        """A single-query search over a FILTERED queryset, the reference's everyday call
+        (assistant/bot/services/context_service/steps/embeddings.py:26-30: bot + status filter, n = 5;
+        assistant/processing/documents/steps/questions.py:124: document__id__lt).  Two int64 columns live in HBM
+        beside the rows; every step builds the allow bitmap on the device (dab_store_build_allow) and searches
+        with it - host query in, host result out.  Checked against the device oracle with the same row mask."""
+        env, torch, L = self.env, self.env.torch, self.env.L
+        from dab_b200 import _lib
+        import device_oracle
+        assert env.world == 1
+        store, dev, n, k = self.store, env.dev, self.hi - self.lo, 5
+        rows = torch.arange(n, device=dev, dtype=torch.int64)
+        store.set_column(0, rows % 4)                      # "bot id"
+        store.set_column(1, rows // 10)                    # "document id" (10 chunks per document)
+        doc_limit = int(0.8 * n) // 10
+        preds = [(0, _lib.DAB_OP_EQ, 1), (1, _lib.DAB_OP_LT, doc_limit)]
+        q_np = self.queries_host[:1].numpy()
+
+        def step():
+            return store.search_host(q_np, k, store.build_allow(preds))
+
+        def timed(fn, reps):
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                r = fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / reps, r
+        for _ in range(warmup):
+            step()
+        ms, (got_s, got_i) = timed(step, steps)
+        ms_bitmap, _ = timed(lambda: store.build_allow(preds), steps)
+        allow = lambda r0, m: ((torch.arange(r0, r0 + m, device=dev) % 4 == 1) & (torch.arange(r0, r0 + m, device=dev) // 10 < doc_limit))
+        wi, ws = device_oracle.oracle_topk(((r, p.to(self.sdtype)) for r, p in self.blocks()), self.queries_dev[:1], k, pad=32, allow=allow)
+        rep = device_oracle.parity_report(torch.from_numpy(got_s).to(dev), torch.from_numpy(got_i).to(dev), wi, ws, k)
+        assert rep["ok"], f"filtered search disagrees with the device oracle: {rep}"
+        bitmap_bytes = n * (2 * 8 + 4) + n // 8
+        return dict(desc=f"{self.w['desc']} - ONE query, top-{k}, queryset filtered on two HBM columns (bot == 1 AND document_id < "
+                         f"{doc_limit}: {0.25 * 0.8:.0%} of the rows pass), bitmap built on the device every step, host buffers in and out",
+                    Q=1, k=k, rows=n, e2e=1e3 / ms, unit="queries/s", e2e_ms_per_step=ms, build_allow_ms=ms_bitmap,
+                    build_allow_hbm_frac=bitmap_bytes / (ms_bitmap * 1e-3) / 1e9 / env.peaks["hbm"],
+                    verified=f"top-{k} identical to the device oracle under the same row mask (worst relative score error {rep['max_rel_score_err']:.1e})")
+
     def roofline(self, m):
         """The `roofline` object of the line from one measurement."""
         peaks, w = self.env.peaks, self.w
@@ -422,6 +467,33 @@ class SearchRun:
 
 class Env:
     pass
+
+
+def vendor_gemm_yardstick(env, rows, dim, Q, reps=100):
+    """What cuBLAS reaches on the scan's OWN shape - [rows x dim] bf16 streamed from HBM times [dim x Q] bf16, about
+    half a second back to back so the power cap settles - against the 8192^3 L2-resident GEMM MEASURED_PEAKS.json
+    quotes as the tensor roof.  It writes the [rows x Q] score matrix, which the scan never does; it selects nothing.
+    A yardstick for roofline.frac of the Q=256 scan, not part of the product path (no library GEMM is)."""
+    torch, dev = env.torch, env.dev
+    a = torch.randn(rows, dim, device=dev, dtype=torch.bfloat16)
+    b = torch.randn(Q, dim, device=dev, dtype=torch.bfloat16)
+    out = torch.empty(rows, Q, device=dev, dtype=torch.bfloat16)
+    for _ in range(5):
+        torch.matmul(a, b.T, out=out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        torch.matmul(a, b.T, out=out)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    tf = 2.0 * rows * dim * Q / (ms * 1e-3) / 1e12
+    del a, b, out
+    torch.cuda.empty_cache()
+    return dict(desc=f"cuBLAS (torch.matmul) bf16 [{rows} x {dim}] x [{dim} x {Q}] -> bf16, {reps} calls back to back: the per-GPU "
+                     "shard shape of the 8-GPU run, as a library GEMM", ms=ms, tflops=tf, frac_of_tensor_peak=tf / env.peaks["tf"],
+                note="yardstick only: the product path calls no library GEMM")
 
 
 def main():
@@ -499,8 +571,12 @@ def main():
             m = run.measure(sw["Q"], args.steps, args.warmup, verify=verify)
             m.pop("_res")
             targets[name] = dict(run.target(m), desc=sw["desc"])
+            if name == "c3":
+                targets["c3_filtered_q1"] = run.measure_filtered(args.steps, args.warmup)
             run.close()
             del run
+
+        targets["vendor_gemm_shard"] = vendor_gemm_yardstick(env, 12_500_000, w["dim"], w["Q"])
 
     # ------------------------------------------------------------------ the headline store
     run = SearchRun(env, w, exchange=args.exchange, path=args.path)

@@ -125,7 +125,7 @@ extern "C" DAB_API int dab_search_noalloc(const void *rows_dev, int rows_dtype, 
 
     SearchScratch sc{};
     sc.qhat = reinterpret_cast<float *>(d->scratch + kOffQhat);
-    sc.qsplit = nullptr;  // only the tensor path uses it; this entry point scores on CUDA cores
+    sc.qbf16 = nullptr;  // only the tensor path uses it; this entry point scores on CUDA cores
     sc.cand = reinterpret_cast<uint64_t *>(d->scratch + kOffCand);
     sc.cand_count = reinterpret_cast<uint32_t *>(d->scratch + kOffCount);
     sc.tau_key = reinterpret_cast<uint64_t *>(d->scratch + kOffTau);

@@ -241,14 +241,14 @@ int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScr
     const int per_slice = (nq + groups - 1) / groups;
     // B comes from the unit-norm fp32 queries (fp32 stores) or from their bf16 copy (bf16 stores); rows past
     // the live queries hold stale data whose columns the epilogue ignores, rows past the buffer read as zero
-    const int q_rows = (f32 ? DAB_MAX_QUERY_BATCH : 2 * DAB_MAX_QUERY_BATCH) - q0;
+    const int q_rows = DAB_MAX_QUERY_BATCH - q0;
     UmmaPlan up;
     if (!plan_umma(sv.dim, per_slice, eb, &up) || groups > num_sms)
         return fail(DAB_E_INVALID, "scan_umma: query block does not fit shared memory");
     alignas(64) CUtensorMap tmap_rows, tmap_q;
     if (int rc = cached_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
     const void *qbase = f32 ? static_cast<const void *>(sc.qhat + (size_t)q0 * sv.dim)
-                            : static_cast<const void *>(sc.qsplit + (size_t)q0 * sv.dim);
+                            : static_cast<const void *>(sc.qbf16 + (size_t)q0 * sv.dim);
     if (int rc = cached_map(&tmap_q, qbase, (uint64_t)q_rows, (uint64_t)sv.dim, (uint32_t)up.n_pad, f32)) return rc;
     auto kernel = f32 ? scan_umma_kernel<true> : scan_umma_kernel<false>;
     static SmemAttrOnce attr_once[2];

@@ -337,8 +337,8 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     if (int rc = cached_map(&tmap_rows, sv.rows, (uint64_t)sv.n, (uint64_t)sv.dim, kTileRows, f32)) return rc;
     // B = the unit-norm fp32 queries (fp32 stores) or their bf16 copy (bf16 stores); rows past the buffer read as zero
     const void *qbase = f32 ? static_cast<const void *>(sc.qhat + (size_t)q0 * sv.dim)
-                            : static_cast<const void *>(sc.qsplit + (size_t)q0 * sv.dim);
-    const uint64_t q_rows = (uint64_t)((f32 ? DAB_MAX_QUERY_BATCH : 2 * DAB_MAX_QUERY_BATCH) - q0);
+                            : static_cast<const void *>(sc.qbf16 + (size_t)q0 * sv.dim);
+    const uint64_t q_rows = (uint64_t)(DAB_MAX_QUERY_BATCH - q0);
     if (int rc = cached_map(&tmap_q, qbase, q_rows, (uint64_t)sv.dim, (uint32_t)(qp.n_pair / 2), f32)) return rc;
     auto kernel = f32 ? scan_umma_quad_kernel<true> : scan_umma_quad_kernel<false>;
     static SmemAttrOnce attr_once[2];

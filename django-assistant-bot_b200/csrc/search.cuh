@@ -12,7 +12,7 @@ constexpr uint64_t kTauMin = 0x007FFFFF00000000ull;
 // DAB_MAX_QUERY_BATCH queries.
 struct SearchScratch {
     float *qhat;            // [256, dim] unit-norm fp32 queries
-    __nv_bfloat16 *qsplit;  // [512, dim] bf16 hi rows then lo rows of qhat (tensor path)
+    __nv_bfloat16 *qbf16;   // [256, dim] qhat rounded to bf16: the B operand of the tensor pass on bf16 stores
     uint64_t *cand;         // [256, kCandCap] candidate keys
     uint32_t *cand_count;   // [256] appended this far (may exceed kCandCap: overflow)
     uint64_t *tau_key;      // [256] current admission threshold (a kept candidate's key)

@@ -12,7 +12,7 @@ size_t search_scratch_bytes(int dim) {
     auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
     size_t b = 0;
     b += up((size_t)DAB_MAX_QUERY_BATCH * dim * sizeof(float));               // qhat
-    b += up((size_t)2 * DAB_MAX_QUERY_BATCH * dim * sizeof(__nv_bfloat16));   // qsplit
+    b += up((size_t)DAB_MAX_QUERY_BATCH * dim * sizeof(__nv_bfloat16));       // qbf16
     b += up((size_t)DAB_MAX_QUERY_BATCH * kCandCap * sizeof(uint64_t));       // cand
     b += up(DAB_MAX_QUERY_BATCH * sizeof(uint32_t));                          // cand_count
     b += up(DAB_MAX_QUERY_BATCH * sizeof(uint64_t));                          // tau_key
@@ -29,8 +29,8 @@ SearchScratch carve_scratch(void *base, int dim) {
     SearchScratch s;
     s.qhat = reinterpret_cast<float *>(p);
     p += up((size_t)DAB_MAX_QUERY_BATCH * dim * sizeof(float));
-    s.qsplit = reinterpret_cast<__nv_bfloat16 *>(p);
-    p += up((size_t)2 * DAB_MAX_QUERY_BATCH * dim * sizeof(__nv_bfloat16));
+    s.qbf16 = reinterpret_cast<__nv_bfloat16 *>(p);
+    p += up((size_t)DAB_MAX_QUERY_BATCH * dim * sizeof(__nv_bfloat16));
     s.cand = reinterpret_cast<uint64_t *>(p);
     p += up((size_t)DAB_MAX_QUERY_BATCH * kCandCap * sizeof(uint64_t));
     s.cand_count = reinterpret_cast<uint32_t *>(p);
@@ -102,13 +102,8 @@ search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int 
     for (int d = tid; d < dim; d += 128) {
         const float v = src[d] * inv;
         sc.qhat[(size_t)qi * dim + d] = v;
-        if (want_split) {
-            // q = hi + lo + r with |r| <= 2^-17 |q|: two bf16 MMAs recover the fp32 query
-            const __nv_bfloat16 hi = __float2bfloat16_rn(v);
-            const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
-            sc.qsplit[(size_t)qi * dim + d] = hi;
-            sc.qsplit[(size_t)(DAB_MAX_QUERY_BATCH + qi) * dim + d] = lo;
-        }
+        // the tensor pass scores with the query rounded to bf16 (the rescoring uses qhat itself)
+        if (want_split) sc.qbf16[(size_t)qi * dim + d] = __float2bfloat16_rn(v);
     }
     if (tid == 0) {
         sc.cand_count[qi] = 0;
