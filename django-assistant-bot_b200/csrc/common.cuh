@@ -152,6 +152,16 @@ __device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gmem_src
                  : "memory");
 }
 
+// Single-thread roles (TMA producer, MMA issuer) must be entered through elect_one(), not `lane == 0`:
+// tcgen05.mma / tcgen05.commit / cp.async.bulk.tensor execute once per WARP and take their operands from
+// uniform registers.  After `lane == 0` ptxas cannot know how many threads are active and wraps every such
+// instruction in an ELECT / R2UR.BROADCAST / branch loop - measured at ~113 cycles per tcgen05.mma instead
+// of the 64-cycle floor of a 256x128x16 MMA (tools/mma_pace.cu).  elect.sync tells it exactly one thread runs.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -90,8 +90,8 @@ scan_simt_kernel(StoreView sv, const uint32_t *__restrict__ allow, SearchScratch
     const long long my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
 
     if (warp == 0) {
-        // ------------------------------------------------ producer
-        if (lane == 0) {
+        // ------------------------------------------------ producer (one elected lane: see elect_one in common.cuh)
+        if (elect_one()) {
             for (long long it = 0; it < my_tiles; it++) {
                 const int s = (int)(it % kStages);
                 const uint32_t ph = (uint32_t)((it / kStages) & 1);

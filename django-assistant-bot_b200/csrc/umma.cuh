@@ -87,16 +87,6 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
         : "memory");
 }
 
-// Single-thread roles (TMA producer, MMA issuer) must be entered through elect_one(), not `lane == 0`:
-// tcgen05.mma / tcgen05.commit / cp.async.bulk.tensor execute once per WARP and take their operands from
-// uniform registers.  After `lane == 0` ptxas cannot know how many threads are active and wraps every such
-// instruction in an ELECT / R2UR.BROADCAST / branch loop - measured at ~113 cycles per tcgen05.mma instead
-// of the 64-cycle floor of a 256x128x16 MMA (tools/mma_pace.cu).  elect.sync tells it exactly one thread runs.
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
 // A value every lane holds identically (loaded from shared/global memory), made PROVABLY uniform: the
 // result of a warp reduction lives in a uniform register.  Call with the whole warp converged.
 __device__ __forceinline__ uint32_t warp_uniform(uint32_t v) { return __reduce_or_sync(0xffffffffu, v); }

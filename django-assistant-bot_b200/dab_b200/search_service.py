@@ -21,6 +21,7 @@ from __future__ import annotations
 
 import asyncio
 import logging
+import time
 from collections import defaultdict
 from typing import Any, Dict, Iterable, List, Optional, Sequence, Tuple
 
@@ -435,9 +436,23 @@ def _table_and_bitmap(qs, field: str):
     return table, table.bitmap_from_pks(pks), model
 
 
+def _log_search(what: str, table, n_queries: int, n: int, bitmap, t0: float, t1: float, t2: float) -> None:
+    """One DEBUG line per device search: sizes, bytes streamed, and where the wall time went - the counterpart of the
+    reference's TimeDebugger around its search (assistant/utils/debug.py:5-30)."""
+    if logger.isEnabledFor(logging.DEBUG):
+        rows = len(table)
+        elem = 2 if table.store.dtype == torch.bfloat16 else 4
+        logger.debug("%s: rows=%d dim=%d queries=%d n=%d filtered=%s corpus_bytes=%d filter_ms=%.3f search_ms=%.3f",
+                     what, rows, table.dim, n_queries, n, bitmap is not None, rows * (table.dim * elem + 4),
+                     (t1 - t0) * 1e3, (t2 - t1) * 1e3)
+
+
 def _search_sync(query_embedding, qs, n: int, field: str):
+    t0 = time.perf_counter()
     table, bitmap, model = _table_and_bitmap(qs, field)
+    t1 = time.perf_counter()
     dist, rows = table.search_rows(query_embedding, n, bitmap)
+    _log_search("_objects_embedding_search", table, 1, n, bitmap, t0, t1, time.perf_counter())
     hits = table.hits(dist[0], rows[0])
     if model is None:
         return hits
@@ -475,8 +490,11 @@ async def embedding_search_sentences(query_embedding: List[float], qs, n: int = 
 
 
 def _search_many_sync(query_embeddings, qs, n: int, field: str):
+    t0 = time.perf_counter()
     table, bitmap, model = _table_and_bitmap(qs, field)
+    t1 = time.perf_counter()
     dist, rows = table.search_rows(query_embeddings, n, bitmap)
+    _log_search("embedding_search_many", table, len(query_embeddings), n, bitmap, t0, t1, time.perf_counter())
     per_query = [table.hits(dist[i], rows[i]) for i in range(dist.shape[0])]
     if model is None:
         return per_query
