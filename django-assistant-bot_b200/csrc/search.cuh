@@ -19,6 +19,7 @@ struct SearchScratch {
     int *active;            // [256] query takes part in the current round
     int *overflowed;        // [256] query overflowed in the current round
     int *inexact_q;         // [256] tensor path: more rows inside the margin than kept -> outputs poisoned (may be null)
+    unsigned int *finish_ticket;  // [256] tensor path: CTAs of a query's rescoring group that are done (may be null)
     SearchCtrl *ctrl;
     // Per-CALL verdict slots {incomplete, inexact}: the finish kernel of every query chunk copies the sticky flags
     // there, so the verdict of a search survives the next search's reset of `ctrl` (two threads on one store).

@@ -19,6 +19,7 @@ size_t search_scratch_bytes(int dim) {
     b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // active
     b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // overflowed
     b += up(DAB_MAX_QUERY_BATCH * sizeof(int));                               // inexact_q
+    b += up(DAB_MAX_QUERY_BATCH * sizeof(unsigned int));                      // finish_ticket
     b += up(sizeof(SearchCtrl));
     return b;
 }
@@ -43,6 +44,8 @@ SearchScratch carve_scratch(void *base, int dim) {
     p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
     s.inexact_q = reinterpret_cast<int *>(p);
     p += up(DAB_MAX_QUERY_BATCH * sizeof(int));
+    s.finish_ticket = reinterpret_cast<unsigned int *>(p);
+    p += up(DAB_MAX_QUERY_BATCH * sizeof(unsigned int));
     s.ctrl = reinterpret_cast<SearchCtrl *>(p);
     s.verdict_dev = nullptr;
     s.verdict_host = nullptr;
@@ -111,6 +114,7 @@ search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int 
         sc.active[qi] = 1;
         sc.overflowed[qi] = 0;
         if (sc.inexact_q) sc.inexact_q[qi] = 0;
+        if (sc.finish_ticket) sc.finish_ticket[qi] = 0;
         if (qi == 0) {
             SearchCtrl c = {};
             if (!first_chunk) {  // a later chunk of the same search call keeps the sticky verdicts
@@ -422,17 +426,80 @@ finish_exact_kernel(SearchScratch sc, StoreView sv, int k, int num_levels, float
 // here with the fp32 query on CUDA cores (fp32 FMA over the stored bf16 row, upcast exactly),
 // re-sorted under (score desc, row asc) and cut to k.
 constexpr int kRescoreThreads = 256;
+constexpr int kRescoreSplit = 8;    // CTAs that share the rescoring of one query's kept candidates
+
+// exact fp32 score of a stored row with the unit-norm fp32 query (bf16 rows upcast exactly); all lanes return it
+__device__ __forceinline__ float rescore_row(const StoreView &sv, const float *__restrict__ q, uint32_t row, int lane) {
+    float acc = 0.f;
+    if (sv.dtype == DAB_BF16) {
+        const uint4 *r = reinterpret_cast<const uint4 *>(static_cast<const __nv_bfloat16 *>(sv.rows) + (size_t)row * sv.dim);
+        for (int c = lane; c < sv.dim / 8; c += 32) {
+            const uint4 v = r[c];
+            const float4 q0 = reinterpret_cast<const float4 *>(q)[2 * c];
+            const float4 q1 = reinterpret_cast<const float4 *>(q)[2 * c + 1];
+            acc = fmaf(bf16_lo(v.x), q0.x, acc);
+            acc = fmaf(bf16_hi(v.x), q0.y, acc);
+            acc = fmaf(bf16_lo(v.y), q0.z, acc);
+            acc = fmaf(bf16_hi(v.y), q0.w, acc);
+            acc = fmaf(bf16_lo(v.z), q1.x, acc);
+            acc = fmaf(bf16_hi(v.z), q1.y, acc);
+            acc = fmaf(bf16_lo(v.w), q1.z, acc);
+            acc = fmaf(bf16_hi(v.w), q1.w, acc);
+        }
+    } else {
+        const float4 *r = reinterpret_cast<const float4 *>(static_cast<const float *>(sv.rows) + (size_t)row * sv.dim);
+        for (int c = lane; c < sv.dim / 4; c += 32) {
+            const float4 v = r[c];
+            const float4 qq = reinterpret_cast<const float4 *>(q)[c];
+            acc = fmaf(v.x, qq.x, acc);
+            acc = fmaf(v.y, qq.y, acc);
+            acc = fmaf(v.z, qq.z, acc);
+            acc = fmaf(v.w, qq.w, acc);
+        }
+    }
+    return warp_sum(acc);
+}
+
+// Grid (kRescoreSplit, Q).  The kept candidates of a query (up to 2048 random rows, ~1.5 KB each) are re-scored by
+// kRescoreSplit CTAs - one CTA per query left Q SMs chasing row latencies one warp-row at a time, 80-130 us at
+// Q = 64 - which overwrite the approximate keys in place with exact ones; the CTA that finishes last (ticket)
+// sorts them under (score desc, row asc) and writes the k outputs.
 __global__ void __launch_bounds__(kRescoreThreads)
 finish_rescore_kernel(SearchScratch sc, StoreView sv, int k, int k_keep, int num_levels,
                       float *__restrict__ out_scores, int64_t *__restrict__ out_ids) {
     extern __shared__ uint64_t keys[];  // [pow2 >= k_keep]
-    const int qi = blockIdx.x;
+    __shared__ int s_last;
+    const int qi = blockIdx.y;
+    const int part = blockIdx.x, parts = gridDim.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // a query with more rows inside the rescoring margin than could be kept is answered with poison (NaN, -1):
     // the caller sees DAB_E_INEXACT and repeats exactly those queries on the CUDA-core path; the rest are final
     const bool lost = sc.inexact_q != nullptr && sc.inexact_q[qi] != 0;
     const bool done = sc.ctrl->cur_level >= num_levels && !lost;
     const int cnt = done ? min((int)sc.cand_count[qi], k_keep) : 0;
+    uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
+    const float *q = sc.qhat + (size_t)qi * sv.dim;
+    // ---- my share of the candidates: warp w of part p takes j = p * warps + w, + parts * warps, ... (two rows in flight)
+    constexpr int kWarps = kRescoreThreads / 32;
+    const int stride = parts * kWarps;
+    for (int j = part * kWarps + warp; j < cnt; j += 2 * stride) {
+        const int j2 = j + stride;
+        const uint32_t row_a = key_row(mine[j]);
+        const uint32_t row_b = j2 < cnt ? key_row(mine[j2]) : row_a;
+        const float sa = rescore_row(sv, q, row_a, lane);
+        const float sb = rescore_row(sv, q, row_b, lane);
+        if (lane == 0) {
+            mine[j] = make_key(sa * sv.inv_norm[row_a], row_a);
+            if (j2 < cnt) mine[j2] = make_key(sb * sv.inv_norm[row_b], row_b);
+        }
+    }
+    // ---- the last CTA of this query's group finishes
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (parts == 1 || atomicAdd(&sc.finish_ticket[qi], 1u) == (unsigned)(parts - 1)) ? 1 : 0;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
     if (qi == 0 && tid == 0) {
         if (sc.ctrl->cur_level < num_levels) sc.ctrl->sticky_incomplete = 1;
         if (sc.ctrl->inexact) sc.ctrl->sticky_inexact = 1;
@@ -440,42 +507,7 @@ finish_rescore_kernel(SearchScratch sc, StoreView sv, int k, int k_keep, int num
     }
     int P = 32;
     while (P < cnt) P <<= 1;
-    const uint64_t *mine = sc.cand + (size_t)qi * kCandCap;
-    const float *q = sc.qhat + (size_t)qi * sv.dim;
-    for (int i = tid; i < P; i += kRescoreThreads) keys[i] = 0ull;
-    __syncthreads();
-    for (int j = warp; j < cnt; j += kRescoreThreads / 32) {
-        const uint32_t row = key_row(mine[j]);
-        float acc = 0.f;
-        if (sv.dtype == DAB_BF16) {
-            const uint4 *r = reinterpret_cast<const uint4 *>(static_cast<const __nv_bfloat16 *>(sv.rows) + (size_t)row * sv.dim);
-            for (int c = lane; c < sv.dim / 8; c += 32) {
-                const uint4 v = r[c];
-                const float4 q0 = reinterpret_cast<const float4 *>(q)[2 * c];
-                const float4 q1 = reinterpret_cast<const float4 *>(q)[2 * c + 1];
-                acc = fmaf(bf16_lo(v.x), q0.x, acc);
-                acc = fmaf(bf16_hi(v.x), q0.y, acc);
-                acc = fmaf(bf16_lo(v.y), q0.z, acc);
-                acc = fmaf(bf16_hi(v.y), q0.w, acc);
-                acc = fmaf(bf16_lo(v.z), q1.x, acc);
-                acc = fmaf(bf16_hi(v.z), q1.y, acc);
-                acc = fmaf(bf16_lo(v.w), q1.z, acc);
-                acc = fmaf(bf16_hi(v.w), q1.w, acc);
-            }
-        } else {
-            const float4 *r = reinterpret_cast<const float4 *>(static_cast<const float *>(sv.rows) + (size_t)row * sv.dim);
-            for (int c = lane; c < sv.dim / 4; c += 32) {
-                const float4 v = r[c];
-                const float4 qq = reinterpret_cast<const float4 *>(q)[c];
-                acc = fmaf(v.x, qq.x, acc);
-                acc = fmaf(v.y, qq.y, acc);
-                acc = fmaf(v.z, qq.z, acc);
-                acc = fmaf(v.w, qq.w, acc);
-            }
-        }
-        acc = warp_sum(acc);
-        if (lane == 0) keys[j] = make_key(acc * sv.inv_norm[row], row);
-    }
+    for (int i = tid; i < P; i += kRescoreThreads) keys[i] = i < cnt ? __ldcg(&mine[i]) : 0ull;
     bitonic_sort_desc<kRescoreThreads>(keys, P);
     const int outn = min(cnt, k);
     for (int j = tid; j < k; j += kRescoreThreads) {
@@ -596,7 +628,8 @@ int launch_finish_rescore(const SearchScratch &sc, const StoreView &sv, int nq, 
                           float *out_scores, int64_t *out_ids, cudaStream_t st) {
     int P = 32;
     while (P < k_keep) P <<= 1;
-    finish_rescore_kernel<<<nq, kRescoreThreads, P * sizeof(uint64_t), st>>>(sc, sv, k, k_keep, num_levels, out_scores, out_ids);
+    const int parts = sc.finish_ticket ? kRescoreSplit : 1;
+    finish_rescore_kernel<<<dim3(parts, nq), kRescoreThreads, P * sizeof(uint64_t), st>>>(sc, sv, k, k_keep, num_levels, out_scores, out_ids);
     DAB_LAUNCH_OK();
     return DAB_OK;
 }
