@@ -195,3 +195,58 @@ def test_tf32_cluster_kernel_on_fp32_stores(N, D, Q, k):
         search_ref.check_topk_parity(S[qi], ids[qi], scores[qi], k)
     assert ids[Q - 1, 0] == 17
     store.close()
+
+
+def test_threads_on_one_store_keep_their_own_verdicts():
+    """Two host threads search the SAME store on their own streams, again and again: thread A's query has 5000
+    near-copies in the corpus (its tensor pass ends DAB_E_INEXACT and the raw answer is poisoned), thread B's
+    queries are ordinary.  Every search keeps its own verdict slot, so A always sees INEXACT and B always sees OK
+    with final answers - whatever the interleaving (the asgiref worker next to another coroutine,
+    assistant/bot/services/context_service/service.py:82-83); and the checked search repeats A's query on the exact
+    path without changing the store for B."""
+    import threading
+    from dab_b200 import _lib, ops
+    L = _lib.lib()
+    g = torch.Generator().manual_seed(77)
+    N, D, k = 60_000, 768, 10
+    rows = torch.randn(N, D, generator=g)
+    qa = torch.randn(1, D, generator=g)
+    qb = torch.randn(6, D, generator=g)
+    idx = torch.randperm(N, generator=g)[:5000]
+    rows[idx] = qa[0] + 0.001 * torch.randn(5000, D, generator=g)
+    store = ops.ChunkStore(N, D, torch.bfloat16, DEV)
+    store.set_path("tcgen05")
+    store.append(rows.to(DEV))
+    stored = rows.to(torch.bfloat16).float().numpy()
+    Sa = search_ref.exact_scores(stored, qa.numpy())
+    Sb = search_ref.exact_scores(stored, qb.numpy())
+    torch.cuda.synchronize()
+    errors = []
+
+    def worker(name, q, S, want_rc):
+        try:
+            stream = torch.cuda.Stream(device=DEV)
+            qd = q.to(DEV)
+            torch.cuda.synchronize()
+            with torch.cuda.stream(stream):
+                for it in range(25):
+                    s, i = store.search_async(qd, k)
+                    rc = L.dab_store_search_status(store._h, stream.cuda_stream)
+                    assert rc == want_rc, (name, it, rc, L.dab_last_error())
+                    if want_rc == _lib.DAB_OK:
+                        for qi in range(q.shape[0]):
+                            search_ref.check_topk_parity(S[qi], i[qi].cpu().numpy(), s[qi].cpu().numpy(), k)
+                    else:
+                        assert torch.isnan(s[0]).all()
+                    if it % 8 == 0:                      # the checked search answers exactly, for both threads
+                        cs, ci = store.search(qd, k)
+                        for qi in range(q.shape[0]):
+                            search_ref.check_topk_parity(S[qi], ci[qi].cpu().numpy(), cs[qi].cpu().numpy(), k)
+        except Exception as e:  # noqa: BLE001
+            errors.append((name, repr(e)))
+
+    ta = threading.Thread(target=worker, args=("A", qa, Sa, _lib.DAB_E_INEXACT))
+    tb = threading.Thread(target=worker, args=("B", qb, Sb, _lib.DAB_OK))
+    ta.start(); tb.start(); ta.join(); tb.join()
+    assert not errors, errors
+    store.close()
