@@ -61,7 +61,8 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     unsigned char *a_smem = b_smem + (size_t)num_kb * b_kb_bytes;  // [stages][128 rows x 128 B]
     float *tau_s = reinterpret_cast<float *>(a_smem + (size_t)stages * kAStageBytes);  // [256]
     float *ntau_s = tau_s + DAB_MAX_QUERY_BATCH;                                        // [256] negated thresholds
-    uint64_t *full = reinterpret_cast<uint64_t *>(ntau_s + DAB_MAX_QUERY_BATCH);
+    uint64_t *tau_key_s = reinterpret_cast<uint64_t *>(ntau_s + DAB_MAX_QUERY_BATCH);  // [256] exact threshold keys
+    uint64_t *full = tau_key_s + DAB_MAX_QUERY_BATCH;
     uint64_t *empty = full + kMaxStages;
     uint64_t *b_full = empty + kMaxStages;
     uint64_t *tmem_full = b_full + 1;                      // [2]
@@ -88,6 +89,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
         const bool live = q < nq && sc.active[q0 + q];
         tau_s[q] = live ? key_score(sc.tau_key[q0 + q]) : INFINITY;
         ntau_s[q] = -tau_s[q];
+        tau_key_s[q] = live ? sc.tau_key[q0 + q] : ~0ull;
     }
     tc_fence_before();
     __syncthreads();
@@ -165,7 +167,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
             mbar_wait_bounded(&tmem_full[a], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pad);
-            epilogue_tile_wl(taddr, (nq + 15) & ~15, rinv, row, tau_s, ntau_s, q0, allow, sc, WarpList{nullptr, nullptr, 0});
+            epilogue_tile_wl(taddr, (nq + 15) & ~15, rinv, row, tau_s, ntau_s, q0, allow, sc, WarpList{nullptr, nullptr, 0}, tau_key_s);
             row = row_next;
             rinv = rinv_next;
             tc_fence_before();
@@ -189,7 +191,7 @@ struct UmmaPlan {
 bool plan_umma(int dim, int nq, int elem_bytes, UmmaPlan *out) {
     const int n_pad = nq <= 16 ? 16 : (nq + 15) / 16 * 16;
     const size_t b_bytes = (size_t)n_pad * (((size_t)dim * elem_bytes + 127) / 128 * 128);   // whole 128-byte k-blocks
-    const size_t fixed = 2 * DAB_MAX_QUERY_BATCH * sizeof(float) + (2 * kMaxStages + 8) * sizeof(uint64_t) + 1024;
+    const size_t fixed = 2 * DAB_MAX_QUERY_BATCH * sizeof(float) + DAB_MAX_QUERY_BATCH * sizeof(uint64_t) + (2 * kMaxStages + 8) * sizeof(uint64_t) + 1024;
     if (b_bytes + fixed + (size_t)kMinStages * kAStageBytes > (size_t)kSmemBudget) return false;
     int stages = (int)(((size_t)kSmemBudget - b_bytes - fixed) / kAStageBytes);
     if (stages > kMaxStages) stages = kMaxStages;

@@ -219,6 +219,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
         const int wq = warp & 3;                               // TMEM lane quarter this warp may read
         // two warps share a lane quarter and split the pair's query columns (whole 16-column slabs each):
         // one warp per quarter was the critical path once the MMAs ran at their floor
+        const bool dense = lvl == 0 && warp_uniform((uint32_t)sc.ctrl->retry) == 0u;   // first visit of level 0: thresholds are all -inf
         const int ncols = (nq + 15) & ~15;
         const int c_split = (ncols / 16 + 1) / 2 * 16;
         const int c_begin = warp >= 8 ? c_split : 0;
@@ -242,7 +243,9 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * n_pair + c_begin);
             const int ew = warp - 4;                                // 0..7
-            const WarpList wl = {pend_key + pl * kPendCap + ew * kWarpCap, pend_q + pl * kPendCap + ew * kWarpCap, kWarpCap};
+            // level 0 admits every row (no threshold exists yet): the lists would overflow at once, so the hits go
+            // straight to the candidate buffers, one reservation per column (epilogue_slab_direct)
+            const WarpList wl = {pend_key + pl * kPendCap + ew * kWarpCap, pend_q + pl * kPendCap + ew * kWarpCap, dense ? 0 : kWarpCap};
             uint32_t hits = 0;
             hits = epilogue_tile_wl(taddr, c_count, rinv, row, tau_s + c_begin, ntau_s + c_begin, q0 + c_begin, allow, sc, wl);
             row = row_next;

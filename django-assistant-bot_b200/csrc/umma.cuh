@@ -197,10 +197,63 @@ __device__ __forceinline__ uint32_t epilogue_slab_wl(const uint32_t (&v)[16], in
     return cnt;
 }
 
+// The same slab without a staging list: hits go straight to the candidate buffers, one atomic PER COLUMN of the slab
+// (lane j reserves the slots of column j for all hitting lanes at once, 16 reservations in flight together) instead
+// of one atomic round trip per hit.  Level 0 admits every row (no threshold yet): 164 k candidates at Q = 64, which
+// the per-hit loop turned into 64 dependent atomic round trips per warp and tile - 134 us for a 5 MB launch.
+// tau_key_s: exact threshold keys (ties on the score are decided by the row) or nullptr when no threshold exists yet.
+__device__ __forceinline__ void epilogue_slab_direct(const uint32_t (&v)[16], int c0, float rinv, long long row,
+                                                     const float *tau_s, const float *ntau_s, const uint64_t *tau_key_s,
+                                                     int q_base, const uint32_t *__restrict__ allow, const SearchScratch &sc) {
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+        const float4 nt = *reinterpret_cast<const float4 *>(ntau_s + c0 + j);
+        float d0, d1, d2, d3;
+        ffma2(d0, d1, __uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]), rinv, nt.x, nt.y);
+        ffma2(d2, d3, __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]), rinv, nt.z, nt.w);
+        m = max3(m, d0, d1);
+        m = max3(m, d2, d3);
+    }
+    if (!__any_sync(0xffffffffu, m >= -1e-6f && rinv > 0.f)) return;
+    uint32_t pass = 0;
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        const float sco = __uint_as_float(v[j]) * rinv;
+        bool ok = sco >= tau_s[c0 + j];
+        if (ok && tau_key_s != nullptr) ok = make_key(sco, (uint32_t)row) > tau_key_s[c0 + j];
+        pass |= (ok ? 1u : 0u) << j;
+    }
+    if (!(rinv > 0.f)) pass = 0;   // zero rows, tombstones and rows past the end never rank
+    if (pass != 0 && allow != nullptr && !((allow[row >> 5] >> (row & 31)) & 1u)) pass = 0;
+    if (!__any_sync(0xffffffffu, pass != 0)) return;
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t col_ballot = 0;       // lane j < 16 keeps which lanes (rows) hit in column j
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        const uint32_t b = __ballot_sync(0xffffffffu, (pass >> j) & 1u);
+        if (lane == j) col_ballot = b;
+    }
+    uint32_t base = 0;
+    if (lane < 16 && col_ballot != 0) base = atomicAdd(&sc.cand_count[q_base + c0 + lane], (uint32_t)__popc(col_ballot));
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        const uint32_t b = __shfl_sync(0xffffffffu, col_ballot, j);
+        const uint32_t bj = __shfl_sync(0xffffffffu, base, j);
+        if ((pass >> j) & 1u) {
+            const uint32_t pos = bj + __popc(b & lt);
+            if (pos < (uint32_t)kCandCap)
+                sc.cand[(size_t)(q_base + c0 + j) * kCandCap + pos] = make_key(__uint_as_float(v[j]) * rinv, (uint32_t)row);
+        }
+    }
+}
+
 // whole accumulator row over `ncols` columns (multiple of 16, warp-uniform); returns the warp's hit count
+// wl.cap == 0: no staging list - hits are written straight to the candidate buffers (epilogue_slab_direct; tau_key_s as there)
 __device__ __forceinline__ uint32_t epilogue_tile_wl(uint32_t taddr, int ncols, float rinv, long long row, const float *tau_s,
                                                      const float *ntau_s, int q_base, const uint32_t *__restrict__ allow,
-                                                     const SearchScratch &sc, const WarpList &wl) {
+                                                     const SearchScratch &sc, const WarpList &wl, const uint64_t *tau_key_s = nullptr) {
     uint32_t cnt = 0;
     if (ncols <= 0) return cnt;
     uint32_t v0[16], v1[16];
@@ -209,11 +262,13 @@ __device__ __forceinline__ uint32_t epilogue_tile_wl(uint32_t taddr, int ncols, 
         tmem_ld_wait();
         const bool second = c0 + 16 < ncols;
         if (second) tmem_ld16(taddr + (uint32_t)(c0 + 16), v1);
-        cnt = epilogue_slab_wl(v0, c0, rinv, row, tau_s, ntau_s, q_base, allow, sc, wl, cnt);
+        if (wl.cap == 0) epilogue_slab_direct(v0, c0, rinv, row, tau_s, ntau_s, tau_key_s, q_base, allow, sc);
+        else cnt = epilogue_slab_wl(v0, c0, rinv, row, tau_s, ntau_s, q_base, allow, sc, wl, cnt);
         if (second) {
             tmem_ld_wait();
             if (c0 + 32 < ncols) tmem_ld16(taddr + (uint32_t)(c0 + 32), v0);
-            cnt = epilogue_slab_wl(v1, c0 + 16, rinv, row, tau_s, ntau_s, q_base, allow, sc, wl, cnt);
+            if (wl.cap == 0) epilogue_slab_direct(v1, c0 + 16, rinv, row, tau_s, ntau_s, tau_key_s, q_base, allow, sc);
+            else cnt = epilogue_slab_wl(v1, c0 + 16, rinv, row, tau_s, ntau_s, q_base, allow, sc, wl, cnt);
         }
     }
     return cnt;
