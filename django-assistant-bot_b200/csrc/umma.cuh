@@ -218,11 +218,12 @@ __device__ __forceinline__ void epilogue_slab_direct(const uint32_t (&v)[16], in
     if (!__any_sync(0xffffffffu, m >= -1e-6f && rinv > 0.f)) return;
     uint32_t pass = 0;
 #pragma unroll
-    for (int j = 0; j < 16; j++) {
-        const float sco = __uint_as_float(v[j]) * rinv;
-        bool ok = sco >= tau_s[c0 + j];
-        if (ok && tau_key_s != nullptr) ok = make_key(sco, (uint32_t)row) > tau_key_s[c0 + j];
-        pass |= (ok ? 1u : 0u) << j;
+    for (int j = 0; j < 16; j += 4) {
+        const float4 tq = *reinterpret_cast<const float4 *>(tau_s + c0 + j);
+        pass |= (__uint_as_float(v[j + 0]) * rinv >= tq.x ? 1u : 0u) << (j + 0);
+        pass |= (__uint_as_float(v[j + 1]) * rinv >= tq.y ? 1u : 0u) << (j + 1);
+        pass |= (__uint_as_float(v[j + 2]) * rinv >= tq.z ? 1u : 0u) << (j + 2);
+        pass |= (__uint_as_float(v[j + 3]) * rinv >= tq.w ? 1u : 0u) << (j + 3);
     }
     if (!(rinv > 0.f)) pass = 0;   // zero rows, tombstones and rows past the end never rank
     if (pass != 0 && allow != nullptr && !((allow[row >> 5] >> (row & 31)) & 1u)) pass = 0;
@@ -236,10 +237,18 @@ __device__ __forceinline__ void epilogue_slab_direct(const uint32_t (&v)[16], in
             const int j = __ffs(pass) - 1;
             pass &= pass - 1;
             const int q = q_base + c0 + j;
-            const uint32_t pos = atomicAdd(&sc.cand_count[q], 1u);
-            if (pos < (uint32_t)kCandCap) sc.cand[(size_t)q * kCandCap + pos] = make_key(__uint_as_float(pick16(v, j)) * rinv, (uint32_t)row);
+            const uint64_t key = make_key(__uint_as_float(pick16(v, j)) * rinv, (uint32_t)row);
+            if (tau_key_s == nullptr || key > tau_key_s[c0 + j]) {   // ties on the score are decided by the row
+                const uint32_t pos = atomicAdd(&sc.cand_count[q], 1u);
+                if (pos < (uint32_t)kCandCap) sc.cand[(size_t)q * kCandCap + pos] = key;
+            }
         }
         return;
+    }
+    if (tau_key_s != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 16; j++)
+            if (((pass >> j) & 1u) && !(make_key(__uint_as_float(v[j]) * rinv, (uint32_t)row) > tau_key_s[c0 + j])) pass &= ~(1u << j);
     }
     const int lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1u;
