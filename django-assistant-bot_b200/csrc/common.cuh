@@ -60,6 +60,13 @@ struct SmemAttrOnce {
     }
 };
 
+// Where a producer kernel writes the per-row store columns when its output rows land directly in a dab_store.
+struct StoreSink {
+    float *inv_norm = nullptr;   // [B] 1/|row| from the stored values (nullptr: the output is not a store)
+    int64_t *ids = nullptr;      // [B]
+    int64_t id_first = 0;
+};
+
 static inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // ---------------------------------------------------------------- candidate keys

@@ -12,7 +12,7 @@
 #include <cooperative_groups.h>
 #include <stdlib.h>
 
-#include "common.cuh"
+#include "store.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -82,7 +82,7 @@ template <bool BF16, int NV>
 __global__ void __launch_bounds__(kPoolThreads)
 pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ mask, int mask_dtype,
                    float *__restrict__ out, __nv_bfloat16 *__restrict__ out_bf16, float *__restrict__ out_inv,
-                   int T, int D, int vecs_per_row, int row_groups) {
+                   int T, int D, int vecs_per_row, int row_groups, StoreSink sink) {
     constexpr int VE = Vec<BF16>::kElems;
     constexpr int U = 8 / NV;  // rows in flight per thread
     extern __shared__ float smem[];
@@ -210,19 +210,39 @@ pool_l2norm_kernel(const uint4 *__restrict__ hidden, const void *__restrict__ ma
         }
         __syncthreads();
         const float inv = s_inv;
+        float stored_ss = 0.f;     // |row|^2 of the values as STORED (ingest: what dab_store_append would compute)
         for (int d = tid; d < D; d += kPoolThreads) {
             const float o = part[d] * inv;
-            out[(size_t)b * D + d] = o;
-            if (out_bf16) out_bf16[(size_t)b * D + d] = __float2bfloat16_rn(o);
+            if (out) out[(size_t)b * D + d] = o;
+            float kept = o;
+            if (out_bf16) {
+                const __nv_bfloat16 ob = __float2bfloat16_rn(o);
+                out_bf16[(size_t)b * D + d] = ob;
+                kept = __bfloat162float(ob);
+            }
+            stored_ss = fmaf(kept, kept, stored_ss);
         }
         if (tid == 0 && out_inv) out_inv[b] = inv;
+        if (sink.inv_norm != nullptr) {
+            // the row lands in a store: its 1/|row| (from the stored values, 0 for a zero row) and its id go with it
+            __syncthreads();               // s_red is reused
+            stored_ss = warp_sum(stored_ss);
+            if (lane == 0) s_red[warp] = stored_ss;
+            __syncthreads();
+            if (tid == 0) {
+                float t = 0.f;
+                for (int w = 0; w < kPoolThreads / 32; w++) t += s_red[w];
+                sink.inv_norm[b] = (t > 0.f && t < INFINITY) ? 1.0f / sqrtf(t) : 0.f;
+                sink.ids[b] = sink.id_first + b;
+            }
+        }
     }
     cluster.sync();  // keep remote shared memory alive until rank 0 has read it
 }
 
 template <bool BF16, int NV>
 int launch_pool(const void *hidden, const void *mask, int mask_dtype, float *out, void *out_bf16, float *out_inv,
-                int64_t B, int64_t T, int64_t D, int S, int vecs_per_row, int row_groups, cudaStream_t stream) {
+                int64_t B, int64_t T, int64_t D, int S, int vecs_per_row, int row_groups, cudaStream_t stream, StoreSink sink) {
     auto kern = pool_l2norm_kernel<BF16, NV>;
     const size_t smem = ((size_t)row_groups * D + D) * sizeof(float);
     if (smem > 48 * 1024) DAB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -240,7 +260,7 @@ int launch_pool(const void *hidden, const void *mask, int mask_dtype, float *out
     cfg.numAttrs = 1;
     DAB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, static_cast<const uint4 *>(hidden), mask, mask_dtype, out,
                                    static_cast<__nv_bfloat16 *>(out_bf16), out_inv, (int)T, (int)D, vecs_per_row,
-                                   row_groups));
+                                   row_groups, sink));
     count_launch();
     return DAB_OK;
 }
@@ -260,11 +280,13 @@ int pool_pick_splits(int64_t B, int64_t T, int row_groups) {
 
 }  // namespace dab
 
-extern "C" DAB_API int dab_pool_l2norm(const void *hidden, int hidden_dtype, const void *mask, int mask_dtype, float *out,
-                               void *out_bf16, float *out_inv, int64_t B, int64_t T, int64_t D, void *stream) {
-    using namespace dab;
+namespace dab {
+// the pool launch behind dab_pool_l2norm and dab_store_ingest (`sink`: where the rows' inverse norms and ids go when
+// the outputs are a store's own memory; `out` may then be NULL)
+static int pool_run(const void *hidden, int hidden_dtype, const void *mask, int mask_dtype, float *out, void *out_bf16,
+                    float *out_inv, int64_t B, int64_t T, int64_t D, void *stream, StoreSink sink) {
     if (B == 0 && T >= 0 && D > 0) return DAB_OK;
-    if (!out || (!hidden && T > 0)) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden/out must not be NULL");
+    if ((!out && !sink.inv_norm) || (!hidden && T > 0)) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden/out must not be NULL");
     if (hidden_dtype != DAB_F32 && hidden_dtype != DAB_BF16) return fail(DAB_E_INVALID, "dab_pool_l2norm: hidden_dtype must be DAB_F32 or DAB_BF16");
     if (mask && (mask_dtype < DAB_MASK_U8 || mask_dtype > DAB_MASK_I64)) return fail(DAB_E_INVALID, "dab_pool_l2norm: bad mask_dtype");
     if (B < 0 || T < 0 || D <= 0) return fail(DAB_E_INVALID, "dab_pool_l2norm: negative size");
@@ -272,7 +294,7 @@ extern "C" DAB_API int dab_pool_l2norm(const void *hidden, int hidden_dtype, con
     if (T > (1 << 24)) return fail(DAB_E_INVALID, "dab_pool_l2norm: T too large");
     const int ve = hidden_dtype == DAB_BF16 ? 8 : 4;
     if (D % ve) return fail(DAB_E_INVALID, "dab_pool_l2norm: D must be a multiple of 4 (fp32) / 8 (bf16)");
-    if (!aligned16(hidden) || !aligned16(out)) return fail(DAB_E_INVALID, "dab_pool_l2norm: pointers must be 16-byte aligned");
+    if (!aligned16(hidden) || (out && !aligned16(out))) return fail(DAB_E_INVALID, "dab_pool_l2norm: pointers must be 16-byte aligned");
     const int vecs = (int)(D / ve);
     int nv = 1, row_groups = 1;
     if (vecs <= kPoolThreads) {
@@ -285,9 +307,41 @@ extern "C" DAB_API int dab_pool_l2norm(const void *hidden, int hidden_dtype, con
     const int S = pool_pick_splits(B, T, row_groups);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool bf = hidden_dtype == DAB_BF16;
-#define DAB_POOL_CASE(BF, NV_) return launch_pool<BF, NV_>(hidden, mask, mask_dtype, out, out_bf16, out_inv, B, T, D, S, vecs, row_groups, st)
+#define DAB_POOL_CASE(BF, NV_) return launch_pool<BF, NV_>(hidden, mask, mask_dtype, out, out_bf16, out_inv, B, T, D, S, vecs, row_groups, st, sink)
     if (nv == 1) { if (bf) DAB_POOL_CASE(true, 1); else DAB_POOL_CASE(false, 1); }
     if (nv == 2) { if (bf) DAB_POOL_CASE(true, 2); else DAB_POOL_CASE(false, 2); }
     if (bf) DAB_POOL_CASE(true, 4); else DAB_POOL_CASE(false, 4);
 #undef DAB_POOL_CASE
+}
+}  // namespace dab
+
+extern "C" DAB_API int dab_pool_l2norm(const void *hidden, int hidden_dtype, const void *mask, int mask_dtype, float *out,
+                               void *out_bf16, float *out_inv, int64_t B, int64_t T, int64_t D, void *stream) {
+    if (!out && B > 0) return dab::fail(DAB_E_INVALID, "dab_pool_l2norm: hidden/out must not be NULL");
+    return dab::pool_run(hidden, hidden_dtype, mask, mask_dtype, out, out_bf16, out_inv, B, T, D, stream, dab::StoreSink{});
+}
+
+extern "C" DAB_API int dab_store_ingest(dab_store *s, const void *hidden, int hidden_dtype, const void *mask, int mask_dtype,
+                                        int64_t B, int64_t T, void *stream) {
+    using namespace dab;
+    if (!s) return fail(DAB_E_INVALID, "dab_store_ingest: store is NULL");
+    if (B < 0) return fail(DAB_E_INVALID, "dab_store_ingest: B < 0");
+    if (B == 0) return DAB_OK;
+    std::lock_guard<std::mutex> g(s->mu);
+    if (s->size + B > s->capacity) return fail(DAB_E_CAPACITY, "dab_store_ingest: store is full");
+    if (s->size > 0 && s->explicit_ids) return fail(DAB_E_INVALID, "dab_store_ingest: the store holds explicit ids; ingested rows get id_base + row");
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    // the kernel's outputs ARE the store: rows [size, size + B), their 1/|row| and ids
+    StoreSink sink;
+    sink.inv_norm = s->inv_norm + s->size;
+    sink.ids = s->ids + s->size;
+    sink.id_first = s->id_base + s->size;
+    float *out_f32 = nullptr;
+    void *out_bf16 = nullptr;
+    if (s->dtype == DAB_BF16) out_bf16 = static_cast<__nv_bfloat16 *>(s->rows) + (size_t)s->size * s->dim;
+    else out_f32 = static_cast<float *>(s->rows) + (size_t)s->size * s->dim;
+    if (int rc = pool_run(hidden, hidden_dtype, mask, mask_dtype, out_f32, out_bf16, nullptr, B, T, s->dim, stream, sink)) return rc;
+    s->explicit_ids = false;
+    s->size += B;
+    return DAB_OK;
 }

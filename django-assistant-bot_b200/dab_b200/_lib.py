@@ -32,6 +32,7 @@ SIGNATURES = {
     "dab_store_dtype": (c_int, [c_void_p]),
     "dab_store_reset": (c_int, [c_void_p]),
     "dab_store_append": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_void_p]),
+    "dab_store_ingest": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_void_p]),
     "dab_store_delete_rows": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "dab_store_compact": (c_int, [c_void_p, POINTER(c_int64), c_void_p]),
     "dab_store_export": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -116,11 +116,14 @@ class B200TransformersEmbedder(AIEmbedder):
         n = 0
         for i in range(0, len(texts), self._max_batch):
             hidden, mask = self._encode_batch(texts[i:i + self._max_batch])
+            if ids is None:
+                n += target.ingest(hidden, mask)          # pool + append in one kernel
+                continue
             if target.dtype == torch.bfloat16:
                 _, rows = ops.pool_l2norm(hidden, mask, want_bf16=True)
             else:
                 rows = ops.pool_l2norm(hidden, mask)
-            target.append(rows, None if ids is None else ids[i:i + rows.shape[0]])
+            target.append(rows, ids[i:i + rows.shape[0]])
             n += rows.shape[0]
         return n
 

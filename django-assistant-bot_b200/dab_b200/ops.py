@@ -186,6 +186,27 @@ class ChunkStore:
             check(lib().dab_store_append(self._h, rows.data_ptr(), _DTYPES[rows.dtype], iptr, rows.shape[0],
                                          _stream(self.device)))
 
+    def ingest(self, hidden: torch.Tensor, mask: Optional[torch.Tensor] = None) -> int:
+        """Pool + normalise ``hidden`` [B,T,dim] (fp32/bf16; ``mask`` [B,T] or None) and append the B rows, in one
+        kernel whose outputs are the store's own rows, inverse norms and ids (``dab_store_ingest``).  Returns B."""
+        _need_cuda(hidden, "hidden")
+        if hidden.dim() != 3 or hidden.shape[2] != self.dim:
+            raise DabError(_lib.DAB_E_DIM, f"hidden must be [B,T,{self.dim}]")
+        if hidden.dtype not in _DTYPES:
+            raise DabError(_lib.DAB_E_INVALID, f"hidden dtype {hidden.dtype} unsupported (fp32 or bf16)")
+        hidden = hidden.contiguous()
+        B, T, _ = hidden.shape
+        mptr, mdt = None, 0
+        if mask is not None:
+            _need_cuda(mask, "mask")
+            if tuple(mask.shape) != (B, T) or mask.dtype not in _MASK_DTYPES:
+                raise DabError(_lib.DAB_E_INVALID, "mask must be [B,T] bool/uint8/int32/int64")
+            mask = mask.contiguous()
+            mptr, mdt = mask.data_ptr(), _MASK_DTYPES[mask.dtype]
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_ingest(self._h, hidden.data_ptr(), _DTYPES[hidden.dtype], mptr, mdt, B, T, _stream(self.device)))
+        return int(B)
+
     def delete_rows(self, rows: torch.Tensor) -> None:
         """Tombstone store rows (row indices, not ids): they are never returned again."""
         _need_cuda(rows, "rows")

@@ -182,9 +182,11 @@ class ShardedStore:
         will scan it.  What ``embedder.embeddings(texts)`` + ``bulk_update(['embedding'])`` do through the
         embedding service and PostgreSQL (assistant/processing/documents/steps/embeddings.py:27-39,57-69).
         ``hidden`` [B,T,D] fp32/bf16 on this rank's device, ``mask`` [B,T].  Returns the rows appended."""
+        if ids is None:
+            return self.local.ingest(hidden, mask)      # one kernel: the pool's outputs are the shard's own rows
         from . import ops
         if self.local.dtype == torch.bfloat16:
-            _, rows = ops.pool_l2norm(hidden, mask, want_bf16=True)      # the kernel's bf16 output is what the store holds
+            _, rows = ops.pool_l2norm(hidden, mask, want_bf16=True)
         else:
             rows = ops.pool_l2norm(hidden, mask)
         self.local.append(rows, ids)
@@ -310,13 +312,7 @@ class LocalShardedStore:
 
     def ingest(self, g: int, hidden: torch.Tensor, mask: Optional[torch.Tensor] = None) -> int:
         """Pool + normalise + append on the GPU that owns the rows (see ``ShardedStore.ingest``)."""
-        from . import ops
-        if self.dtype == torch.bfloat16:
-            _, rows = ops.pool_l2norm(hidden, mask, want_bf16=True)
-        else:
-            rows = ops.pool_l2norm(hidden, mask)
-        self.shards[g].append(rows)
-        return int(rows.shape[0])
+        return self.shards[g].ingest(hidden, mask)
 
     def search_host(self, queries, k: int):
         import numpy as np

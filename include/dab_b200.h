@@ -129,6 +129,16 @@ DAB_API int dab_store_reset(dab_store *s);
 DAB_API int dab_store_append(dab_store *s, const void *rows_dev, int rows_dtype, const int64_t *ids_dev_or_null,
                      int64_t n, void *stream);
 /*
+ * Ingest: pool + normalise encoder hidden states and append the rows to the store in ONE kernel - the write path
+ * `embedder.embeddings(texts)` -> `bulk_update(['embedding'])` of
+ * assistant/processing/documents/steps/embeddings.py:27-39,57-69 without a round trip through host memory or a second
+ * pass over the rows: the pool kernel's outputs are the store's own rows [size, size+B) (bf16 or fp32), their 1/|row|
+ * (from the stored values) and their ids (id_base + row; stores with explicit ids are refused).
+ *   hidden [B,T,dim] hidden_dtype, mask [B,T] mask_dtype or NULL: as dab_pool_l2norm.
+ */
+DAB_API int dab_store_ingest(dab_store *s, const void *hidden_dev, int hidden_dtype, const void *mask_dev, int mask_dtype,
+                             int64_t B, int64_t T, void *stream);
+/*
  * Delete rows (tombstones): the rows stay in place but are never returned again - their stored
  * inverse norm becomes -0.0, which every scan treats like a zero vector.  Replaces the deletes of
  * document finalisation (older documents of a wiki removed, assistant/processing/tasks.py:67-74).

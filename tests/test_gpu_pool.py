@@ -87,3 +87,40 @@ def test_ingest_pools_and_appends_into_the_owning_shard():
         s, i = sh.search(torch.from_numpy(want[5:6]).to(DEV), 1)
         assert i[0, 0].item() == 5 and abs(s[0, 0].item() - 1.0) < 1e-3
         sh.close()
+
+
+@pytest.mark.parametrize("store_dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("hidden_dtype", [torch.float32, torch.bfloat16])
+def test_store_ingest_equals_pool_then_append(store_dtype, hidden_dtype):
+    """dab_store_ingest (the pool kernel writing straight into the store) leaves exactly what dab_pool_l2norm followed
+    by dab_store_append leaves: the same stored rows, the same 1/|row| (taken from the stored values), the same ids."""
+    from dab_b200 import ops
+    g = torch.Generator().manual_seed(23)
+    B, T, D = 37, 33, 768
+    hidden = torch.randn(B, T, D, generator=g).to(hidden_dtype).to(DEV)
+    lengths = torch.randint(0, T + 1, (B,), generator=g)          # a zero-length text too: a zero row, never ranked
+    lengths[3] = 0
+    mask = (torch.arange(T)[None] < lengths[:, None]).to(torch.int64).to(DEV)
+    a = ops.ChunkStore(100, D, store_dtype, DEV, id_base=40)
+    b = ops.ChunkStore(100, D, store_dtype, DEV, id_base=40)
+    for st in (a, b):
+        st.append(torch.randn(5, D, generator=g).to(DEV))          # rows already there: the ingest continues after them
+    a_rows_before = a.export(0, 5)[0]
+    assert a.ingest(hidden, mask) == B and len(a) == 5 + B
+    if store_dtype == torch.bfloat16:
+        _, rows = ops.pool_l2norm(hidden, mask, want_bf16=True)
+    else:
+        rows = ops.pool_l2norm(hidden, mask)
+    b.append(rows)
+    ra, ia, da = a.export(0, 5 + B)
+    rb, ib, db = b.export(0, 5 + B)
+    assert torch.equal(ra[5:], rb[5:]) and torch.equal(da, db) and torch.equal(ra[:5], a_rows_before)
+    np.testing.assert_allclose(ia.cpu().numpy(), ib.cpu().numpy(), rtol=2e-7, atol=0)
+    assert ia[5 + 3].item() == 0.0 and da[-1].item() == 40 + 5 + B - 1
+    q = ra[10:11].float()
+    sa, ida = a.search(q, 3)
+    sb, idb = b.search(q, 3)
+    assert torch.equal(ida, idb) and ida[0, 0].item() == 40 + 10
+    with pytest.raises(ops.DabError):
+        a.ingest(torch.randn(100, T, D, device=DEV), None)          # beyond capacity
+    a.close(); b.close()
