@@ -103,8 +103,9 @@ def test_store_ingest_equals_pool_then_append(store_dtype, hidden_dtype):
     mask = (torch.arange(T)[None] < lengths[:, None]).to(torch.int64).to(DEV)
     a = ops.ChunkStore(100, D, store_dtype, DEV, id_base=40)
     b = ops.ChunkStore(100, D, store_dtype, DEV, id_base=40)
+    first = torch.randn(5, D, generator=g).to(DEV)
     for st in (a, b):
-        st.append(torch.randn(5, D, generator=g).to(DEV))          # rows already there: the ingest continues after them
+        st.append(first)                                           # rows already there: the ingest continues after them
     a_rows_before = a.export(0, 5)[0]
     assert a.ingest(hidden, mask) == B and len(a) == 5 + B
     if store_dtype == torch.bfloat16:
