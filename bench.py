@@ -316,13 +316,12 @@ class SearchRun:
         out_host_i = torch.empty(Q, k, dtype=torch.int64).pin_memory()
         gs = torch.empty(world, Q, k, dtype=torch.float32, device=dev) if world > 1 else None
         gi = torch.empty(world, Q, k, dtype=torch.int64, device=dev) if world > 1 else None
-        status_ptr = L.dab_store_status_dev(store._h)
-
         def step_device():
             if sh.peer is not None:                         # one fused publish/wait/gather/merge kernel over NVLink
                 slot = sh.peer.next_slot(Q, k)
                 store.search_async(q_dev, k, out=slot)
-                return sh.peer.merge(Q, k, status_ptr)
+                # every search has its own verdict slot: ask for it after the search was enqueued
+                return sh.peer.merge(Q, k, L.dab_store_status_dev(store._h))
             s, i = store.search_async(q_dev, k)
             if world > 1:
                 dist.all_gather_into_tensor(gs, s)
