@@ -16,7 +16,9 @@ assistant/ai/services/ai_service.py:51-74, same name (typo included), same ``gpu
 """
 from __future__ import annotations
 
+import asyncio
 import os
+import threading
 from abc import ABC, abstractmethod
 from typing import List, Optional, Sequence
 
@@ -69,6 +71,7 @@ class B200TransformersEmbedder(AIEmbedder):
         self._max_batch = int(max_batch)
         self._unit_norm = unit_norm
         self._max_length = max_length
+        self._forward_lock = threading.Lock()      # one encoder forward at a time per embedder
 
     def _encode_batch(self, texts: Sequence[str]):
         kw = {}
@@ -102,9 +105,16 @@ class B200TransformersEmbedder(AIEmbedder):
         return torch.cat(outs, 0)
 
     async def embeddings(self, input: List[str]) -> List[List[float]]:
+        """Same contract as the reference; the blocking GPU work runs in a worker thread so the event loop of the
+        embedding service keeps answering while a batch is in flight (the reference computes inside ``async def``,
+        gpu_service/main.py:75-86 with transformers.py:15-29, which stalls every other request of the worker)."""
         if not input:
             return []
-        return self.embed_tensor(input).tolist()
+
+        def work():
+            with self._forward_lock:
+                return self.embed_tensor(input).tolist()
+        return await asyncio.to_thread(work)
 
     def embed_into(self, store, texts: Sequence[str], ids: Optional[torch.Tensor] = None) -> int:
         """The ingest path in one call: encode, pool + normalise, and append the rows to ``store`` (a
