@@ -124,6 +124,45 @@ class DeviceTable:
             self._meta.setdefault(k, []).extend(list(v))
         self._cols.clear()
 
+    def load_queryset(self, qs, field: str = "embedding", columns: Optional[Dict[str, str]] = None, batch: int = 8192,
+                      document_field: Optional[str] = "document_id", text_field: Optional[str] = "text",
+                      order_field: Optional[str] = "order") -> int:
+        """Bulk load from the database column: every row of ``qs`` whose ``field`` is not NULL, streamed in chunks
+        (``qs.exclude(<field>__isnull=True).values_list(...).iterator(chunk_size=batch)``) and appended with its
+        pk, document id, text, order and the filter columns asked for - ``columns`` maps the name used in
+        ``ChunkQuerySet.filter`` to the ORM path it is read from, e.g.
+        ``{"document__wiki__bot": "document__wiki__bot_id", "document__processing__status": "document__processing__status"}``
+        (the filters of assistant/bot/services/context_service/steps/embeddings.py:26-29).  For
+        ``Document.content_embedding`` (assistant/storage/models.py:13) pass ``document_field="pk"``,
+        ``text_field=None``, ``order_field=None``.  The store is a cache of that column: this is how it is (re)built."""
+        columns = dict(columns or {})
+        names = ["pk", field] + [f for f in (document_field, text_field, order_field) if f] + list(columns.values())
+        rows = qs.exclude(**{f"{field}__isnull": True}).values_list(*names)
+        rows = rows.iterator(chunk_size=batch) if hasattr(rows, "iterator") else iter(rows)
+        total = 0
+        while True:
+            chunk = []
+            for r in rows:
+                chunk.append(r)
+                if len(chunk) == batch:
+                    break
+            if not chunk:
+                break
+            cols = list(zip(*chunk))
+            pos = 2
+            docs = texts = orders = None
+            if document_field:
+                docs, pos = cols[pos], pos + 1
+            if text_field:
+                texts, pos = cols[pos], pos + 1
+            if order_field:
+                orders, pos = cols[pos], pos + 1
+            meta = {name: list(cols[pos + i]) for i, name in enumerate(columns)}
+            emb = np.asarray([np.asarray(e, dtype=np.float32) for e in cols[1]], dtype=np.float32)
+            self.add(list(cols[0]), emb, docs, texts, orders, **meta)
+            total += len(chunk)
+        return total
+
     def delete(self, pks: Iterable[int]) -> int:
         """Remove rows by pk: what ``Document.objects.filter(...).delete()`` cascades to on finalisation
         (assistant/processing/tasks.py:67-74).  Rows become tombstones on the device (never returned

@@ -325,3 +325,44 @@ def test_delete_and_snapshot_roundtrip(tmp_path, dtype):
     np.testing.assert_allclose([h.distance for h in hits2], [h.distance for h in hits], atol=1e-7)
     t.close()
     t2.close()
+
+
+def test_bulk_load_from_a_django_style_queryset():
+    """DeviceTable.load_queryset: the device store (re)built from the database column - NULL embeddings skipped
+    (the column is nullable, assistant/storage/models.py:23), rows streamed in chunks with their pk, document id,
+    text, order and filter columns; then a filtered search over what was loaded."""
+    from dab_b200 import search_service as ss
+    rng = np.random.default_rng(8)
+    n, dim = 1000, 64
+    emb = rng.standard_normal((n, dim)).astype(np.float32)
+    records = [dict(pk=10 + i, embedding=None if i % 9 == 0 else emb[i].tolist(), document_id=i // 5, text=f"s{i}", order=i % 5,
+                    document__wiki__bot_id=i % 3) for i in range(n)]
+
+    class QS:
+        def __init__(self, recs):
+            self.recs = recs
+
+        def exclude(self, **kw):
+            assert kw == {"embedding__isnull": True}
+            return QS([r for r in self.recs if r["embedding"] is not None])
+
+        def values_list(self, *names):
+            self.names = names
+            return self
+
+        def iterator(self, chunk_size=2000):
+            assert chunk_size == 128
+            return iter([tuple(r[nm] for nm in self.names) for r in self.recs])
+
+    t = ss.DeviceTable(n, dim, torch.float32, DEV)
+    loaded = t.load_queryset(QS(records), "embedding", columns={"document__wiki__bot": "document__wiki__bot_id"}, batch=128)
+    keep = np.array([i for i in range(n) if i % 9 != 0])
+    assert loaded == len(keep) == len(t)
+    q = emb[keep[17]] + 0.01
+    hits = asyncio.run(ss._objects_embedding_search(q.tolist(), ss.ChunkQuerySet(t).filter(document__wiki__bot=keep[17] % 3), n=5))
+    S = search_ref.exact_scores(emb[keep], q[None])[0]
+    want, wsc = search_ref.rank_topk(S, 5, (keep % 3) == keep[17] % 3)
+    assert [h.pk for h in hits] == [10 + int(keep[w]) for w in want]
+    assert hits[0].text == f"s{keep[17]}" and hits[0].document_id == keep[17] // 5 and hits[0].order == keep[17] % 5
+    np.testing.assert_allclose([h.distance for h in hits], 1 - wsc, atol=2e-6)
+    t.close()
