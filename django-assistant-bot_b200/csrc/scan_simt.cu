@@ -63,6 +63,7 @@ scan_simt_kernel(StoreView sv, const uint32_t *__restrict__ allow, SearchScratch
                  const __grid_constant__ LevelPlan plan) {
     constexpr int VE = RowVec<BF16>::kElems;
     extern __shared__ __align__(128) unsigned char smem[];
+    pdl_enter();
     const int lvl = sc.ctrl->cur_level;
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];
@@ -192,8 +193,8 @@ int launch_one(const StoreView &sv, const uint32_t *allow, const SearchScratch &
     long long max_tiles = 0;
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
-    kern<<<grid, kScanThreads, smem, st>>>(sv, allow, sc, q0, nq, plan);
-    DAB_LAUNCH_OK();
+    DAB_CUDA_OK(launch_chained(kern, dim3(grid), dim3(kScanThreads), smem, st, sv, allow, sc, q0, nq, plan));
+    count_launch();
     return DAB_OK;
 }
 

@@ -39,6 +39,7 @@ scan_umma_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __grid_con
     // F32: fp32 store and fp32 queries, scored with kind::tf32 (K = 8 per MMA); a k-block is
     // 128 bytes of a row either way: 64 bf16 or 32 fp32
     extern __shared__ unsigned char smem_raw[];
+    pdl_enter();
     const int lvl = (int)warp_uniform((uint32_t)sc.ctrl->cur_level);
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];
@@ -259,8 +260,9 @@ int launch_scan_umma(const StoreView &sv, const uint32_t *allow, const SearchScr
     for (int l = 0; l < plan.num_levels; l++) max_tiles = plan.tiles_in_level[l] > max_tiles ? plan.tiles_in_level[l] : max_tiles;
     const long long seqs = max_tiles < num_sms / groups ? max_tiles : num_sms / groups;
     const int grid = (int)seqs * groups;
-    kernel<<<grid, kThreads, up.smem, st>>>(tmap_rows, tmap_q, sv, allow, sc, q0, nq, up.n_pad, up.stages, up.tmem_cols, groups, plan);
-    DAB_LAUNCH_OK();
+    DAB_CUDA_OK(launch_chained(kernel, dim3(grid), dim3(kThreads), up.smem, st, tmap_rows, tmap_q, sv, allow, sc, q0, nq, up.n_pad, up.stages,
+                               up.tmem_cols, groups, plan));
+    count_launch();
     return DAB_OK;
 }
 

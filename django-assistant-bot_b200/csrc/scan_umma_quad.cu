@@ -56,6 +56,7 @@ scan_umma_quad_kernel(const __grid_constant__ CUtensorMap tmap_rows, const __gri
                       const uint32_t *__restrict__ allow, SearchScratch sc, int q0_all, int nq_all, int n_pair, int stages,
                       int tmem_cols, int num_pairs, int acc_stages, const __grid_constant__ LevelPlan plan) {
     extern __shared__ unsigned char smem_raw[];
+    pdl_enter();
     const int lvl = (int)warp_uniform((uint32_t)sc.ctrl->cur_level);
     if (lvl >= plan.num_levels) return;
     const long long ntiles = plan.tiles_in_level[lvl];  // super-tiles of 256 rows
@@ -353,13 +354,15 @@ int launch_scan_umma_quad(const StoreView &sv, const uint32_t *allow, const Sear
     cfg.blockDim = dim3(kThreads, 1, 1);
     cfg.dynamicSmemBytes = qp.smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = kCluster;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // see pdl_enter (common.cuh)
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     int max_clusters = 0;
     DAB_CUDA_OK(occ_cache[f32 ? 1 : 0].get(&max_clusters, kernel, &cfg, kCluster));
     if (max_clusters < 1) return fail(DAB_E_CUDA, "scan_umma_quad: no 4-CTA cluster fits on this device");

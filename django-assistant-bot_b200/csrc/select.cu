@@ -88,6 +88,7 @@ namespace {
 // ---------------------------------------------------------------- begin: normalise queries, reset state
 __global__ void __launch_bounds__(128)
 search_begin_kernel(SearchScratch sc, const float *__restrict__ q, int dim, int want_split, int first_chunk) {
+    pdl_enter();
     const int qi = blockIdx.x;
     const int tid = threadIdx.x;
     __shared__ float red[4];
@@ -259,6 +260,7 @@ compact_kernel(SearchScratch sc, int nq, int k, int k_cap, float margin, int num
     extern __shared__ uint64_t keys[];  // [kCandCap]
     __shared__ int s_scan[kCompactThreads / 32];
     __shared__ int s_is_last;
+    pdl_enter();
     const int qi = blockIdx.x;
     const int tid = threadIdx.x;
     SearchCtrl *ctrl = sc.ctrl;
@@ -396,6 +398,7 @@ __device__ __forceinline__ void publish_verdict(const SearchScratch &sc) {
 __global__ void __launch_bounds__(128)
 finish_exact_kernel(SearchScratch sc, StoreView sv, int k, int num_levels, float *__restrict__ out_scores,
                     int64_t *__restrict__ out_ids) {
+    pdl_enter();
     const int qi = blockIdx.x;
     const bool done = sc.ctrl->cur_level >= num_levels;
     const int cnt = done ? min((int)sc.cand_count[qi], k) : 0;
@@ -469,6 +472,7 @@ finish_rescore_kernel(SearchScratch sc, StoreView sv, int k, int k_keep, int num
                       float *__restrict__ out_scores, int64_t *__restrict__ out_ids) {
     extern __shared__ uint64_t keys[];  // [pow2 >= k_keep]
     __shared__ int s_last;
+    pdl_enter();
     const int qi = blockIdx.y;
     const int part = blockIdx.x, parts = gridDim.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -599,8 +603,8 @@ merge_topk_kernel(const float *__restrict__ gs, const int64_t *__restrict__ gi, 
 
 int launch_search_begin(const SearchScratch &sc, const float *q_dev, int nq, int dim, bool want_split, cudaStream_t st,
                         bool first_chunk) {
-    search_begin_kernel<<<nq, 128, 0, st>>>(sc, q_dev, dim, want_split ? 1 : 0, first_chunk ? 1 : 0);
-    DAB_LAUNCH_OK();
+    DAB_CUDA_OK(launch_chained(search_begin_kernel, dim3(nq), dim3(128), 0, st, sc, q_dev, dim, want_split ? 1 : 0, first_chunk ? 1 : 0));
+    count_launch();
     return DAB_OK;
 }
 
@@ -612,15 +616,15 @@ int launch_compact_margin(const SearchScratch &sc, int nq, int k, int k_cap, flo
     const int smem = kCandCap * sizeof(uint64_t);
     static SmemAttrOnce attr_once;
     DAB_CUDA_OK(attr_once.ensure(compact_kernel, smem));
-    compact_kernel<<<nq, kCompactThreads, smem, st>>>(sc, nq, k, k_cap, margin, num_levels);
-    DAB_LAUNCH_OK();
+    DAB_CUDA_OK(launch_chained(compact_kernel, dim3(nq), dim3(kCompactThreads), smem, st, sc, nq, k, k_cap, margin, num_levels));
+    count_launch();
     return DAB_OK;
 }
 
 int launch_finish_exact(const SearchScratch &sc, const StoreView &sv, int nq, int k, int num_levels, float *out_scores,
                         int64_t *out_ids, cudaStream_t st) {
-    finish_exact_kernel<<<nq, 128, 0, st>>>(sc, sv, k, num_levels, out_scores, out_ids);
-    DAB_LAUNCH_OK();
+    DAB_CUDA_OK(launch_chained(finish_exact_kernel, dim3(nq), dim3(128), 0, st, sc, sv, k, num_levels, out_scores, out_ids));
+    count_launch();
     return DAB_OK;
 }
 
@@ -629,8 +633,9 @@ int launch_finish_rescore(const SearchScratch &sc, const StoreView &sv, int nq, 
     int P = 32;
     while (P < k_keep) P <<= 1;
     const int parts = sc.finish_ticket ? kRescoreSplit : 1;
-    finish_rescore_kernel<<<dim3(parts, nq), kRescoreThreads, P * sizeof(uint64_t), st>>>(sc, sv, k, k_keep, num_levels, out_scores, out_ids);
-    DAB_LAUNCH_OK();
+    DAB_CUDA_OK(launch_chained(finish_rescore_kernel, dim3(parts, nq), dim3(kRescoreThreads), P * sizeof(uint64_t), st, sc, sv, k, k_keep,
+                               num_levels, out_scores, out_ids));
+    count_launch();
     return DAB_OK;
 }
 
