@@ -66,36 +66,84 @@ class ChunkRow:
         return f"ChunkRow(id={self.id}, document_id={self.document_id}, distance={self.distance:.6f})"
 
 
+class _Grow:
+    """A NumPy array that grows by doubling: the host-side columns of a table with 10^8 rows cannot be Python lists."""
+
+    def __init__(self, dtype):
+        self.a = np.empty(1024, dtype=dtype)
+        self.n = 0
+
+    def extend(self, values) -> None:
+        v = np.asarray(values, dtype=self.a.dtype).reshape(-1)
+        need = self.n + v.shape[0]
+        if need > self.a.shape[0]:
+            cap = self.a.shape[0]
+            while cap < need:
+                cap *= 2
+            b = np.empty(cap, dtype=self.a.dtype)
+            b[:self.n] = self.a[:self.n]
+            self.a = b
+        self.a[self.n:need] = v
+        self.n = need
+
+    def view(self) -> np.ndarray:
+        return self.a[:self.n]
+
+    def keep(self, idx: np.ndarray) -> None:
+        kept = self.a[:self.n][idx]
+        self.a, self.n = kept.copy(), kept.shape[0]
+        if self.a.shape[0] == 0:
+            self.a = np.empty(1024, dtype=kept.dtype)
+
+
 class DeviceTable:
     """Device-resident copy of one embedding column: ``Sentence.embedding``,
     ``Question.embedding`` (assistant/storage/models.py:32-58) or ``Document.content_embedding``
     (:13).  Rows with a NULL embedding are simply not added (the column is nullable, :23).
 
-    Host side keeps what the ORM would: pk, document_id, text, order, and any columns the
-    reference filters on (e.g. ``document__wiki__bot``), as NumPy arrays aligned with store rows.
+    Host side keeps what the ORM would - pk, document_id, order, the columns the reference filters on
+    (e.g. ``document__wiki__bot``; non-numeric values dictionary-encoded) - as growable NumPy int64 arrays aligned
+    with the store rows (8 bytes per row and column, not a Python object), and the texts only if any were given.
     """
 
     def __init__(self, capacity: int, dim: int = EMBEDDING_DIM, dtype: torch.dtype = torch.float32, device=None):
         self.store = ops.ChunkStore(capacity, dim, dtype, device)
         self.dim = dim
         self.device = self.store.device
-        self._pks: List[int] = []
-        self._doc: List[int] = []
-        self._text: List[Optional[str]] = []
-        self._order: List[int] = []
-        self._meta: Dict[str, List[Any]] = {}
-        self._cols: Dict[str, np.ndarray] = {}
-        self._row_of_pk: Dict[int, int] = {}
-        self._doc_dev: Optional[torch.Tensor] = None     # device copy of the document_id column (lazy)
-        # filter columns in HBM (dab_store_set_column): name -> (device column index, rows uploaded so far);
-        # values that are not integers (status strings ...) are dictionary-encoded per column
+        self._pks = _Grow(np.int64)
+        self._doc = _Grow(np.int64)
+        self._order = _Grow(np.int64)
+        self._dead = _Grow(np.bool_)                      # store rows turned into tombstones
+        self._n_dead = 0
+        self._text: Optional[List[Optional[str]]] = None  # allocated when the first text arrives
+        self._meta: Dict[str, _Grow] = {}                 # filter columns: int64 values or dictionary codes
+        self._codes: Dict[str, Dict[Any, int]] = {}       # value -> code of the dictionary-encoded columns
+        self._decode: Dict[str, List[Any]] = {}           # code -> value
+        self._pk_sorted: Optional[Tuple[np.ndarray, np.ndarray]] = None   # (sorted pks, their rows), built on demand
+        self._doc_dev: Optional[torch.Tensor] = None      # device copy of the document_id column (lazy)
+        # filter columns in HBM (dab_store_set_column): name -> [device column index, rows uploaded so far]
         self._dev_cols: Dict[str, List[int]] = {}
-        self._codes: Dict[str, Dict[Any, int]] = {}
-        self._deleted: set = set()                        # store rows turned into tombstones
         self.documents: Dict[int, Any] = {}
 
     def __len__(self):
-        return len(self._pks)
+        return self._pks.n
+
+    def _encode(self, name: str, values) -> np.ndarray:
+        """Column values as int64: integers as they are, anything else through the column's dictionary."""
+        arr = np.asarray(values)
+        if arr.dtype.kind in "iub" and name not in self._codes:
+            return arr.astype(np.int64)
+        if len(self) and name in self._meta and name not in self._codes:
+            raise DabError(1, f"filter column {name!r} held integers so far; it cannot switch to other values")
+        codes, decode = self._codes.setdefault(name, {}), self._decode.setdefault(name, [])
+        out = np.empty(arr.shape[0], dtype=np.int64)
+        for i, v in enumerate(arr.tolist()):
+            c = codes.get(v)
+            if c is None:
+                c = codes[v] = len(decode)
+                decode.append(v)
+            out[i] = c
+        return out
 
     def add(self, pks: Sequence[int], embeddings, document_ids: Optional[Sequence[int]] = None,
             texts: Optional[Sequence[str]] = None, orders: Optional[Sequence[int]] = None, **meta) -> None:
@@ -112,17 +160,23 @@ class DeviceTable:
         known = set(self._meta)
         if len(self) and set(meta) != known:
             raise DabError(1, f"filter columns changed: {sorted(meta)} vs {sorted(known)}")
+        encoded = {k: self._encode(k, v) for k, v in meta.items()}
+        for k, v in encoded.items():
+            if v.shape[0] != n:
+                raise DabError(1, f"filter column {k!r} has {v.shape[0]} values for {n} rows")
         self.store.append(emb.to(self.device))
-        base = len(self._pks)
-        for i, pk in enumerate(pks):
-            self._row_of_pk[int(pk)] = base + i
-        self._pks.extend(int(p) for p in pks)
-        self._doc.extend(int(d) for d in (document_ids if document_ids is not None else [0] * n))
-        self._text.extend(texts if texts is not None else [None] * n)
-        self._order.extend(int(o) for o in (orders if orders is not None else range(n)))
-        for k, v in meta.items():
-            self._meta.setdefault(k, []).extend(list(v))
-        self._cols.clear()
+        before = len(self)
+        self._pks.extend(np.asarray(pks, dtype=np.int64))
+        self._doc.extend(np.zeros(n, np.int64) if document_ids is None else np.asarray(document_ids, dtype=np.int64))
+        self._order.extend(np.arange(n, dtype=np.int64) if orders is None else np.asarray(orders, dtype=np.int64))
+        self._dead.extend(np.zeros(n, np.bool_))
+        if texts is not None and self._text is None and any(t is not None for t in texts):
+            self._text = [None] * before
+        if self._text is not None:
+            self._text.extend(texts if texts is not None else [None] * n)
+        for k, v in encoded.items():
+            self._meta.setdefault(k, _Grow(np.int64)).extend(v)
+        self._pk_sorted = None
 
     def load_queryset(self, qs, field: str = "embedding", columns: Optional[Dict[str, str]] = None, batch: int = 8192,
                       document_field: Optional[str] = "document_id", text_field: Optional[str] = "text",
@@ -163,75 +217,82 @@ class DeviceTable:
             total += len(chunk)
         return total
 
+    def _rows_of_pks(self, pks: Iterable[int]) -> np.ndarray:
+        """Store rows of the given pks (unknown and already deleted pks are skipped) through a sorted index."""
+        want = np.unique(np.fromiter((int(p) for p in pks), dtype=np.int64))
+        if self._pk_sorted is None:
+            order = np.argsort(self._pks.view(), kind="stable")
+            self._pk_sorted = (self._pks.view()[order], order)
+        spk, rows = self._pk_sorted
+        pos = np.searchsorted(spk, want)
+        ok = (pos < spk.shape[0])
+        ok[ok] &= spk[pos[ok]] == want[ok]
+        found = rows[pos[ok]]
+        return found[~self._dead.view()[found]]
+
     def delete(self, pks: Iterable[int]) -> int:
         """Remove rows by pk: what ``Document.objects.filter(...).delete()`` cascades to on finalisation
         (assistant/processing/tasks.py:67-74).  Rows become tombstones on the device (never returned
-        again) and are masked out of every later queryset; returns how many rows were removed."""
-        rows = [self._row_of_pk.pop(int(p)) for p in pks if int(p) in self._row_of_pk]
-        if not rows:
+        again, excluded from every bitmap); returns how many rows were removed."""
+        rows = self._rows_of_pks(pks)
+        if rows.shape[0] == 0:
             return 0
-        self.store.delete_rows(torch.as_tensor(rows, dtype=torch.int64).to(self.device))
-        self._deleted.update(rows)
-        self._cols.clear()
-        return len(rows)
+        self.store.delete_rows(torch.from_numpy(rows.astype(np.int64)).to(self.device))
+        self._dead.view()[rows] = True
+        self._n_dead += int(rows.shape[0])
+        return int(rows.shape[0])
 
     def compact(self) -> int:
         """Physically drop the tombstones (what VACUUM does for the table after the cascade deletes):
-        the device store moves the surviving rows down in order and the host columns follow with the
-        same survivors, so store row ``i`` is again row ``i`` of every column.  Returns rows removed."""
-        if not self._deleted:
+        the device store moves the surviving rows (and its filter columns) down in order and the host columns
+        follow with the same survivors, so store row ``i`` is again row ``i`` of every column.  Returns rows removed."""
+        if not self._n_dead:
             return 0
-        live = self.live_mask()
         for name in list(self._dev_cols):                # every row's values on the device before the rows move
             self._device_column(name)
+        keep = np.flatnonzero(~self._dead.view())
         removed = self.store.compact()
-        if removed != len(self._deleted) or len(self.store) != int(live.sum()):
-            raise DabError(1, f"compaction removed {removed} rows, {len(self._deleted)} were tombstoned")
-        keep = np.flatnonzero(live).tolist()
-        self._pks = [self._pks[i] for i in keep]
-        self._doc = [self._doc[i] for i in keep]
-        self._text = [self._text[i] for i in keep]
-        self._order = [self._order[i] for i in keep]
-        self._meta = {k: [v[i] for i in keep] for k, v in self._meta.items()}
-        self._row_of_pk = {pk: i for i, pk in enumerate(self._pks)}
-        self._deleted = set()
+        if removed != self._n_dead or len(self.store) != keep.shape[0]:
+            raise DabError(1, f"compaction removed {removed} rows, {self._n_dead} were tombstoned")
+        for col in (self._pks, self._doc, self._order, self._dead, *self._meta.values()):
+            col.keep(keep)
+        if self._text is not None:
+            self._text = [self._text[i] for i in keep.tolist()]
+        self._n_dead = 0
+        self._pk_sorted = None
         self._doc_dev = None
-        self._cols.clear()
         for name in self._dev_cols:                      # the HBM columns were compacted with the rows
-            self._dev_cols[name][1] = len(self._pks)
+            self._dev_cols[name][1] = len(self)
         return removed
 
     def live_mask(self) -> Optional[np.ndarray]:
-        if not self._deleted:
-            return None
-        m = np.ones(len(self), dtype=np.bool_)
-        m[list(self._deleted)] = False
-        return m
+        return ~self._dead.view() if self._n_dead else None
 
     def save(self, path: str) -> None:
-        """Snapshot of the shard: rows in the store's dtype + the host columns, as one ``.npz``.
-        The device store is a cache of the DB column (it can always be rebuilt from PostgreSQL);
-        the snapshot only avoids re-reading and re-uploading 768 floats per row at start-up."""
+        """Snapshot of the shard: rows in the store's dtype + the host columns, as one ``.npz`` of plain arrays
+        (loading never unpickles anything).  The device store is a cache of the DB column (it can always be rebuilt
+        from PostgreSQL); the snapshot only avoids re-reading and re-uploading 768 floats per row at start-up."""
         n = len(self)
         blocks = []
         for r0 in range(0, n, 1 << 18):
             rows, _, _ = self.store.export(r0, min(1 << 18, n - r0))
             blocks.append(rows.view(torch.int16).cpu().numpy() if rows.dtype == torch.bfloat16 else rows.cpu().numpy())
         data = np.concatenate(blocks, 0) if blocks else np.zeros((0, self.dim), np.float32)
-        meta = {}
-        for k, v in self._meta.items():
-            arr = np.asarray(v)
-            if arr.dtype == object:
-                raise DabError(1, f"filter column {k!r} mixes value types; snapshots hold numbers or strings only")
-            meta[f"meta__{k}"] = arr
-        # texts as one UTF-8 blob + lengths (-1 = NULL): plain arrays only, so loading never unpickles anything
-        enc = [None if t is None else t.encode("utf-8") for t in self._text]
+        extra = {}
+        for k, col in self._meta.items():
+            extra[f"meta__{k}"] = col.view()
+            if k in self._decode:
+                values = np.asarray(self._decode[k])
+                if values.dtype == object:
+                    raise DabError(1, f"filter column {k!r} mixes value types; snapshots hold numbers or strings only")
+                extra[f"dict__{k}"] = values
+        texts = self._text if self._text is not None else [None] * n
+        enc = [None if t is None else t.encode("utf-8") for t in texts]   # one UTF-8 blob + lengths (-1 = NULL)
         np.savez(path, rows=data, bf16=np.asarray(self.store.dtype == torch.bfloat16), dim=np.asarray(self.dim),
-                 pks=np.asarray(self._pks, dtype=np.int64), docs=np.asarray(self._doc, dtype=np.int64),
-                 orders=np.asarray(self._order, dtype=np.int64),
+                 pks=self._pks.view(), docs=self._doc.view(), orders=self._order.view(),
                  text_blob=np.frombuffer(b"".join(e for e in enc if e is not None), dtype=np.uint8),
                  text_len=np.asarray([-1 if e is None else len(e) for e in enc], dtype=np.int64),
-                 deleted=np.asarray(sorted(self._deleted), dtype=np.int64), **meta)
+                 deleted=np.flatnonzero(self._dead.view()).astype(np.int64), **extra)
 
     @classmethod
     def load(cls, path: str, capacity: Optional[int] = None, device=None) -> "DeviceTable":
@@ -239,7 +300,12 @@ class DeviceTable:
         bf16 = bool(z["bf16"])
         n = z["rows"].shape[0]
         t = cls(max(capacity or n, 1), int(z["dim"]), torch.bfloat16 if bf16 else torch.float32, device)
-        meta = {k[len("meta__"):]: z[k] for k in z.files if k.startswith("meta__")}
+        meta = {}
+        for k in z.files:
+            if k.startswith("meta__"):
+                name = k[len("meta__"):]
+                codes = z[k]
+                meta[name] = z[f"dict__{name}"][codes] if f"dict__{name}" in z.files else codes
         blob, lens = z["text_blob"].tobytes(), z["text_len"]
         ends = np.cumsum(np.maximum(lens, 0))
         texts = [None if l < 0 else blob[e - l:e].decode("utf-8") for l, e in zip(lens.tolist(), ends.tolist())]
@@ -247,26 +313,12 @@ class DeviceTable:
             r1 = min(n, r0 + (1 << 18))
             blk = torch.from_numpy(z["rows"][r0:r1])
             emb = blk.view(torch.bfloat16) if bf16 else blk
-            t.add(z["pks"][r0:r1].tolist(), emb, z["docs"][r0:r1].tolist(), texts[r0:r1],
-                  z["orders"][r0:r1].tolist(), **{k: v[r0:r1].tolist() for k, v in meta.items()})
-        dead = z["deleted"].tolist()
-        if dead:
-            t.delete([t._pks[r] for r in dead])
+            t.add(z["pks"][r0:r1], emb, z["docs"][r0:r1], texts[r0:r1], z["orders"][r0:r1],
+                  **{k: v[r0:r1].tolist() for k, v in meta.items()})
+        dead = z["deleted"]
+        if dead.shape[0]:
+            t.delete(z["pks"][dead].tolist())
         return t
-
-    def column(self, name: str) -> np.ndarray:
-        if name not in self._cols:
-            if name in ("pk", "id"):
-                self._cols[name] = np.asarray(self._pks, dtype=np.int64)
-            elif name in ("document_id", "document__id", "document"):
-                self._cols[name] = np.asarray(self._doc, dtype=np.int64)
-            elif name == "order":
-                self._cols[name] = np.asarray(self._order, dtype=np.int64)
-            elif name in self._meta:
-                self._cols[name] = np.asarray(self._meta[name])
-            else:
-                raise DabError(1, f"unknown filter column {name!r}; known: pk, document_id, order, {sorted(self._meta)}")
-        return self._cols[name]
 
     def bitmap_from_mask(self, mask: np.ndarray) -> torch.Tensor:
         """Utility for callers that already hold a row mask (not used on the query path)."""
@@ -274,14 +326,6 @@ class DeviceTable:
 
     # -- queryset filters on the device -------------------------------------------------------------
     _ALIASES = {"id": "pk", "document__id": "document_id", "document": "document_id"}
-
-    def _encode(self, name: str, values) -> np.ndarray:
-        """Column values as int64: integers as they are, anything else through a per-column dictionary."""
-        arr = np.asarray(values)
-        if arr.dtype.kind in "iub":
-            return arr.astype(np.int64)
-        codes = self._codes.setdefault(name, {})
-        return np.asarray([codes.setdefault(v, len(codes)) for v in arr.tolist()], dtype=np.int64)
 
     def _encode_operand(self, name: str, value) -> Optional[int]:
         """The int64 a filter value compares as; None = a value this column has never held."""
@@ -303,8 +347,7 @@ class DeviceTable:
         idx, done = self._dev_cols[name]
         n = len(self)
         if done < n:
-            vals = torch.from_numpy(self._encode(name, host[done:n])).to(self.device)
-            self.store.set_column(idx, vals, done)
+            self.store.set_column(idx, torch.from_numpy(np.ascontiguousarray(host.view()[done:n])).to(self.device), done)
             self._dev_cols[name][1] = n
         return idx
 
@@ -369,7 +412,7 @@ class DeviceTable:
         if len(self) == 0:
             return []
         if self._doc_dev is None or self._doc_dev.numel() != len(self):
-            self._doc_dev = torch.as_tensor(np.asarray(self._doc, dtype=np.int64)).to(self.device)
+            self._doc_dev = torch.from_numpy(np.ascontiguousarray(self._doc.view())).to(self.device)
         if int(n) > ops._lib.DAB_MAX_K:
             raise DabError(ops._lib.DAB_E_CAPACITY, f"max_scores_n * top_n * 10 = {n} exceeds DAB_MAX_K = {ops._lib.DAB_MAX_K}")
         k = int(n)
@@ -380,10 +423,11 @@ class DeviceTable:
 
     def hits(self, dist_row: np.ndarray, rows_row: np.ndarray) -> List[ChunkRow]:
         out = []
+        pks, docs, orders = self._pks.view(), self._doc.view(), self._order.view()
         for d, r in zip(dist_row, rows_row):
             if r < 0:
                 break  # fewer matching rows than n, like [:n] on a shorter queryset
-            out.append(ChunkRow(self._pks[r], self._doc[r], self._text[r], self._order[r], float(d)))
+            out.append(ChunkRow(int(pks[r]), int(docs[r]), None if self._text is None else self._text[r], int(orders[r]), float(d)))
         return out
 
     def close(self):
@@ -436,7 +480,7 @@ class ChunkQuerySet:
 
     def count(self) -> int:
         if not self._preds:
-            return len(self.table) - len(getattr(self.table, "_deleted", ()))
+            return len(self.table) - getattr(self.table, "_n_dead", 0)
         bm = self.allow_bitmap()
         n = len(self.table)
         bits = (bm.view(torch.uint8)[:, None] >> torch.arange(8, device=bm.device, dtype=torch.uint8)[None, :]) & 1
