@@ -185,3 +185,26 @@ def test_http_clients_and_factory_against_the_endpoint(monkeypatch):
     finally:
         server.should_exit = True
         th.join(timeout=5)
+
+
+def test_device_table_host_columns_without_a_gpu():
+    """The host side of DeviceTable (growable NumPy columns, pk -> row index by sorted search, dictionary codes for
+    non-numeric filter values) is plain NumPy and can be checked here; the device side is in tests/test_gpu_*.py."""
+    from dab_b200.search_service import DeviceTable, _Grow
+    g = _Grow(np.int64)
+    for i in range(5):
+        g.extend(np.arange(i * 700, (i + 1) * 700))
+    assert g.n == 3500 and (g.view() == np.arange(3500)).all()
+    g.keep(np.arange(0, 3500, 7))
+    assert g.n == 500 and g.view()[3] == 21
+    t = DeviceTable.__new__(DeviceTable)                      # no store: only the host-side helpers are exercised
+    t._pks, t._dead, t._pk_sorted = _Grow(np.int64), _Grow(np.bool_), None
+    t._codes, t._decode, t._meta = {}, {}, {}
+    pks = np.array([50, 10, 40, 20, 30], dtype=np.int64)
+    t._pks.extend(pks)
+    t._dead.extend(np.array([False, False, True, False, False]))
+    assert sorted(t._rows_of_pks([10, 20, 40, 99, 10]).tolist()) == [1, 3]      # 40 is already deleted, 99 unknown
+    assert t._encode("bot", [3, 5, 3]).tolist() == [3, 5, 3] and "bot" not in t._codes
+    assert t._encode("status", ["done", "new", "done"]).tolist() == [0, 1, 0]
+    assert t._encode("status", ["new", "failed"]).tolist() == [1, 2] and t._decode["status"] == ["done", "new", "failed"]
+    assert t._encode_operand("status", "failed") == 2 and t._encode_operand("status", "never") is None
