@@ -432,6 +432,56 @@ class SearchRun:
                     build_allow_hbm_frac=bitmap_bytes / (ms_bitmap * 1e-3) / 1e9 / env.peaks["hbm"],
                     verified=f"top-{k} identical to the device oracle under the same row mask (worst relative score error {rep['max_rel_score_err']:.1e})")
 
+    def measure_docsearch(self, steps, warmup):
+        """The reference's document-level query (`embedding_search`, assistant/rag/services/search_service.py:111-152,
+        called with max_scores_n = 5, top_n = 5 from steps/embeddings.py:47): the n = 250 nearest chunks of ONE query,
+        grouped per document ON THE DEVICE (dab_doc_aggregate), <= 5 (document, score) pairs back to the host."""
+        env, torch = self.env, self.env.torch
+        from dab_b200 import ops
+        import device_oracle
+        assert env.world == 1
+        store, dev, n = self.store, env.dev, self.hi - self.lo
+        max_scores_n, top_n = 5, 5
+        k = max_scores_n * top_n * 10                      # search_service.py:129-131
+        # 40 chunks per document, interleaved (row r belongs to document r % (n/40)) so that several chunks of one
+        # document can be near a query; the query is aimed at a row so that some document qualifies
+        n_docs = max(1, n // 40)
+        doc_of_row = torch.arange(n, device=dev, dtype=torch.int64) % n_docs
+        q_host = self.queries_host[:1].clone().pin_memory()
+        qd = q_host.to(dev)
+        out_host = torch.empty(2, top_n, dtype=torch.float64).pin_memory()
+
+        def step():
+            q = q_host.to(dev, non_blocking=True)
+            scores, rows = store.search(q, k)              # checked search (verdict read = the only sync besides the result)
+            docs, dscores = ops.doc_aggregate(scores, rows, doc_of_row, max_scores_n, top_n)
+            out_host[0].copy_(docs[0], non_blocking=True)
+            out_host[1].copy_(dscores[0], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return scores, rows, docs, dscores
+
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            scores, rows, docs, dscores = step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        wi, ws = device_oracle.oracle_topk(((r, p.to(self.sdtype)) for r, p in self.blocks()), qd, k, pad=64)
+        rep = device_oracle.parity_report(scores, rows, wi, ws, k)
+        assert rep["ok"], f"n=250 search disagrees with the device oracle: {rep}"
+        want = device_oracle.doc_level_scores((rows[0] % n_docs).tolist(), (1.0 - scores[0].double()).tolist(), max_scores_n, top_n)
+        got = [(int(d), float(s)) for d, s in zip(docs[0].tolist(), dscores[0].tolist()) if d >= 0]
+        assert [d for d, _ in got] == [d for d, _ in want] and all(abs(a[1] - b[1]) < 1e-5 for a, b in zip(got, want)), (got, want)
+        return dict(desc=f"{self.w['desc']} - the reference's document-level query: ONE query, n = {k} nearest chunks, grouped per "
+                         f"document on the device (max_scores_n = {max_scores_n}, top_n = {top_n}), host query in, <= {top_n} documents out",
+                    Q=1, k=k, rows=n, e2e=1e3 / ms, unit="queries/s", e2e_ms_per_step=ms, documents_returned=len(got),
+                    verified=f"top-{k} chunks identical to the device oracle; document ranking identical to the restated grouping "
+                             f"of search_service.py:133-150 ({len(got)} documents)")
+
     def roofline(self, m):
         """The `roofline` object of the line from one measurement."""
         peaks, w = self.env.peaks, self.w
@@ -572,6 +622,7 @@ def main():
             targets[name] = dict(run.target(m), desc=sw["desc"])
             if name == "c3":
                 targets["c3_filtered_q1"] = run.measure_filtered(args.steps, args.warmup)
+                targets["c3_docsearch_q1"] = run.measure_docsearch(args.steps, args.warmup)
             run.close()
             del run
 

@@ -152,3 +152,19 @@ def parity_report(got_scores: torch.Tensor, got_ids: torch.Tensor, want_ids: tor
     out["ok"] = all(out[x] == 0 for x in ("slot_mismatch", "bad_empty_slot", "id_not_in_oracle_list", "order_violations",
                                            "score_violations", "duplicate_ids"))
     return out
+
+
+def doc_level_scores(hit_doc_ids, hit_distances, max_scores_n: int, top_n: int):
+    """The grouping of ``embedding_search`` (assistant/rag/services/search_service.py:133-150) restated for the
+    checker: hits in rank order are grouped per document, documents with fewer than ``max_scores_n`` hits are
+    dropped, score = 1 - mean of the first ``max_scores_n`` distances, best ``top_n`` (ties: first appearance)."""
+    groups, order = {}, []
+    for d, dist in zip(hit_doc_ids, hit_distances):
+        d = int(d)
+        if d not in groups:
+            groups[d] = []
+            order.append(d)
+        groups[d].append(float(dist))
+    scored = [(d, 1 - sum(groups[d][:max_scores_n]) / max_scores_n) for d in order if len(groups[d]) >= max_scores_n]
+    scored.sort(key=lambda x: x[1], reverse=True)
+    return scored[:top_n]
