@@ -443,9 +443,9 @@ class SearchRun:
         store, dev, n = self.store, env.dev, self.hi - self.lo
         max_scores_n, top_n = 5, 5
         k = max_scores_n * top_n * 10                      # search_service.py:129-131
-        # 40 chunks per document, interleaved (row r belongs to document r % (n/40)) so that several chunks of one
-        # document can be near a query; the query is aimed at a row so that some document qualifies
-        n_docs = max(1, n // 40)
+        # synthetic random rows have no document structure: 40 interleaved "documents" (row r belongs to document
+        # r % 40) give the grouping something to do - ~6 of the 250 hits per document, several documents qualify
+        n_docs = 40
         doc_of_row = torch.arange(n, device=dev, dtype=torch.int64) % n_docs
         q_host = self.queries_host[:1].clone().pin_memory()
         qd = q_host.to(dev)
