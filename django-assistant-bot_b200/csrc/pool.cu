@@ -75,7 +75,7 @@ constexpr int kTokChunk = 2048;  // tokens whose mask is compacted into shared m
 // robin.  Masked-out rows cost nothing (never loaded), work is balanced however ragged the batch
 // is, and no load waits on a mask load.
 // Measured on the C5 batch (256 x 512 x 1024 fp32, lengths 16..512): cluster sizes 2 / 4 / 8 give 55.9 / 54.5 / 56.8 us,
-// and 4 rows in flight per thread with 6 CTAs per SM 57.8 us against 54.4 us for this form (8 rows, 4 CTAs per SM):
+// and 4 / 12 / 16 rows in flight per thread 57.8 / 56.2 / 63.6 us against 54.4 us for this form (8 rows, 4 CTAs per SM):
 // the step is bounded by the ~13 us every launch of this size pays for ramp-up and tail (dense batches: 86 us at
 // B = 256, 305 us at B = 1024, i.e. 7.4 TB/s marginal), not by the access pattern.
 template <bool BF16, int NV>
