@@ -115,3 +115,15 @@ def test_raw_c_abi_predicates_and_errors():
     s, i = store.search(q, 5, bm)
     assert want[(i.cpu().numpy() - 500).ravel()].all()
     store.close()
+
+
+def test_stateful_table_fuzz_slice():
+    """A fixed-seed slice of tools/fuzz_table.py: random add / delete / compact / snapshot sequences on a DeviceTable,
+    every step followed by a filtered search checked against a NumPy model of the table."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_table
+    rng = np.random.default_rng(424242)
+    for s in range(40):
+        fuzz_table.one_sequence(rng, s)
