@@ -816,6 +816,9 @@ def bench_pool(args, w, env):
                 dtype="f32", data="synthetic", config=dict(m["config"], workload=args.workload, desc=w["desc"]),
                 e2e=m["e2e"], gpu_launches=m["launches"], clocks=clocks, roofline=m["roofline"], verified=m["verified"],
                 pool_ms=m["pool_ms"])
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        line["roofline"]["traffic"] = json.load(open(tpath)).get(args.workload)
     if "cpu_baseline" in m:
         line["cpu_baseline"] = m["cpu_baseline"]
     print(json.dumps(line))
