@@ -63,6 +63,16 @@ build_allow_kernel(const __grid_constant__ PredArgs pa, const float *__restrict_
     }
 }
 
+// queryset given as a list of store rows: one bit per listed row (tombstones and out-of-range rows are skipped)
+__global__ void scatter_allow_kernel(const int64_t *__restrict__ rows, int64_t n, const float *__restrict__ inv_norm, int64_t n_rows,
+                                     uint32_t *__restrict__ bitmap) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t r = rows[i];
+    if (r < 0 || r >= n_rows || __float_as_uint(inv_norm[r]) == 0x80000000u) return;
+    atomicOr(&bitmap[r >> 5], 1u << (r & 31));
+}
+
 }  // namespace
 }  // namespace dab
 
@@ -119,6 +129,20 @@ extern "C" DAB_API int dab_store_build_allow(dab_store *s, const dab_predicate *
     if (blocks > cap) blocks = cap;
     build_allow_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(pa, s->inv_norm, s->explicit_ids ? s->ids : nullptr,
                                                                                        s->id_base, s->size, bitmap_out_dev);
+    DAB_LAUNCH_OK();
+    return DAB_OK;
+}
+
+extern "C" DAB_API int dab_store_allow_from_rows(dab_store *s, const int64_t *rows_dev, int64_t n, uint32_t *bitmap_out_dev, void *stream) {
+    if (!s) return fail(DAB_E_INVALID, "dab_store_allow_from_rows: store is NULL");
+    if (n < 0 || (n > 0 && !rows_dev) || !bitmap_out_dev) return fail(DAB_E_INVALID, "dab_store_allow_from_rows: bad argument");
+    std::lock_guard<std::mutex> g(s->mu);
+    if (s->size == 0) return DAB_OK;
+    DAB_CUDA_OK(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    DAB_CUDA_OK(cudaMemsetAsync(bitmap_out_dev, 0, (size_t)((s->size + 31) / 32) * sizeof(uint32_t), st));
+    if (n == 0) return DAB_OK;
+    scatter_allow_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rows_dev, n, s->inv_norm, s->size, bitmap_out_dev);
     DAB_LAUNCH_OK();
     return DAB_OK;
 }

@@ -45,6 +45,7 @@ SIGNATURES = {
     "dab_store_set_path": (c_int, [c_void_p, c_int]),
     "dab_store_set_column": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int64, c_void_p]),
     "dab_store_build_allow": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "dab_store_allow_from_rows": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "dab_merge_topk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "dab_doc_aggregate": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                   c_void_p]),

@@ -269,6 +269,16 @@ class ChunkStore:
         bitmap._dab_keep = keep
         return bitmap
 
+    def allow_from_rows(self, rows: torch.Tensor) -> torch.Tensor:
+        """The allow bitmap with one bit per listed STORE ROW (int64 CUDA tensor): a device scatter, O(len(rows))."""
+        _need_cuda(rows, "rows")
+        rows = rows.to(torch.int64).contiguous()
+        bitmap = torch.empty(max((len(self) + 31) // 32, 1), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib().dab_store_allow_from_rows(self._h, rows.data_ptr() if rows.numel() else None, rows.numel(),
+                                                  bitmap.data_ptr(), _stream(self.device)))
+        return bitmap
+
     # -- read side
     def search_async(self, queries: torch.Tensor, k: int, allow_bitmap: Optional[torch.Tensor] = None,
                      out: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, *, path: int = -1, spare_rounds: int = -1):

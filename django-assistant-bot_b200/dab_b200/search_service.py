@@ -382,9 +382,11 @@ class DeviceTable:
         return bitmap
 
     def bitmap_from_pks(self, pks: Iterable[int]) -> torch.Tensor:
-        """The queryset as a pk list (what a Django QuerySet can give us): ``pk IN (sorted pks)`` on the device."""
-        arr = np.unique(np.fromiter((int(p) for p in pks), dtype=np.int64))
-        return self.build_bitmap([(self._device_column("pk"), 6, torch.from_numpy(arr).to(self.device))])
+        """The queryset as a pk list (what a Django QuerySet can give us): the pks are mapped to store rows through
+        the sorted pk index (vectorised, O(len(pks) log N) on the host) and scattered into the bitmap on the device
+        (``dab_store_allow_from_rows``, O(len(pks))) - nothing touches all N rows."""
+        rows = self._rows_of_pks(pks)
+        return self.store.allow_from_rows(torch.from_numpy(np.ascontiguousarray(rows, dtype=np.int64)).to(self.device))
 
     def search_rows(self, query_embeddings, n: int, bitmap: Optional[torch.Tensor] = None):
         """(distances [Q, n'] float64 ascending, store rows [Q, n'] int64); n' <= n."""

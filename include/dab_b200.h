@@ -235,6 +235,10 @@ typedef struct dab_predicate {
 } dab_predicate;
 DAB_API int dab_store_set_column(dab_store *s, int column, const int64_t *values_dev, int64_t row0, int64_t n, void *stream);
 DAB_API int dab_store_build_allow(dab_store *s, const dab_predicate *preds, int n_pred, uint32_t *bitmap_out_dev, void *stream);
+/* The allow bitmap of a queryset given as a LIST of store rows (a Django queryset arrives as its pks; the caller maps
+ * pk -> row): the bitmap is cleared and one bit is set per listed row - O(list), not O(rows), for the reference's
+ * usual small result sets.  Tombstoned and out-of-range rows are skipped; duplicates are harmless. */
+DAB_API int dab_store_allow_from_rows(dab_store *s, const int64_t *rows_dev, int64_t n, uint32_t *bitmap_out_dev, void *stream);
 
 /*
  * k-way merge of per-shard top-k lists (after the all-gather).  New in the build: the

@@ -104,6 +104,13 @@ def test_raw_c_abi_predicates_and_errors():
     bm = store.build_allow([(3, _lib.DAB_OP_EQ, 4), (_lib.DAB_COL_ID, _lib.DAB_OP_GE, 1000)])
     want = (np.arange(N) % 10 == 4) & (np.arange(N) + 500 >= 1000)
     np.testing.assert_array_equal(_unpack(bm, N), want)
+    # a queryset as a list of rows: device scatter, tombstones and out-of-range rows skipped, duplicates harmless
+    store.delete_rows(torch.tensor([7], device=DEV))
+    listed = torch.tensor([3, 7, 64, 999, 3, 1000, -1], device=DEV)
+    want_rows = np.zeros(N, bool)
+    want_rows[[3, 64, 999]] = True
+    np.testing.assert_array_equal(_unpack(store.allow_from_rows(listed), N), want_rows)
+    assert not _unpack(store.allow_from_rows(torch.zeros(0, dtype=torch.int64, device=DEV)), N).any()
     with pytest.raises(ops.DabError):
         store.build_allow([(5, _lib.DAB_OP_EQ, 1)])          # never set
     with pytest.raises(ops.DabError):
